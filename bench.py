@@ -1,0 +1,342 @@
+#!/usr/bin/env python
+"""Headline benchmark: env-steps/s including perspectives at d=7 (BASELINE.json configs[1]).
+
+  python bench.py --gpus N --steps K --warmup W            # B200 arm (this repo's CUDA engine)
+  python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on the host cores
+
+One "step" = one fused actor iteration over every env of the rank: on-device random action -> step
+(incremental syndrome, reward, terminal) -> auto-reset of finished envs -> all perspectives of the new
+states written as the float32 (sumP,2,d,d) network-input tensor + positions + counts/offsets.
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "env_steps_per_sec_incl_perspectives_d7"
+UNIT = "env-steps/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=("b200", "reference"))
+    ap.add_argument("--d", type=int, default=7)
+    ap.add_argument("--p", type=float, default=0.1)
+    ap.add_argument("--envs", type=int, default=65536, help="envs per GPU (weak scaling)")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--cpu-envs", type=int, default=8192, help="envs in the bounded CPU sample")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return ("d=%d p=%g %d envs/GPU random actions: step + auto-reset + perspectives (fp32)"
+            % (a.d, a.p, a.envs))
+
+
+def b_alg(d, n_envs, sum_p, s=4):
+    """Algorithmic bytes of one whole step (SURVEY.md section 8d / BASELINE.md section 4)."""
+    per_env = 2 * ((4 * d * d + 7) // 8) + 2 * ((2 * d * d + 7) // 8) + 30
+    return n_envs * per_env + sum_p * (2 * d * d * s + 4)
+
+
+def write_kernel_bytes(d, n_envs, sum_p):
+    """Algorithmic bytes of one persp_write_kernel launch: perspectives + positions out, syndrome + offsets."""
+    return sum_p * (2 * d * d * 4 + 4) + n_envs * (((2 * d * d + 7) // 8) + 8)
+
+
+# ----------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu_index, self.proc, self.path = gpu_index, None, None
+
+    def __enter__(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+        return self
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if not self.path or not os.path.exists(self.path):
+            return out
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------------------------
+def cpu_arm(a, seconds, n_envs, threads=0):
+    """Time the oracle's C port of the same loop on the host cores (bounded sample)."""
+    from oracle import c_oracle as C
+    loop = C.ActorLoop(a.d, n_envs, a.p, seed=a.seed, nthreads=threads)
+    loop.run(2)                                  # warm caches / page in the buffers
+    t0 = time.perf_counter()
+    loop.run(2)
+    per_step = max((time.perf_counter() - t0) / 2, 1e-6)
+    steps = max(3, int(seconds / per_step))
+    c0 = loop.counters.copy()
+    t0 = time.perf_counter()
+    loop.run(steps)
+    dt = time.perf_counter() - t0
+    c = loop.counters - c0
+    return {"value": float(c[0]) / dt, "unit": UNIT, "cores": loop.nthreads, "kind": "port",
+            "sample": "%d envs x %d steps, d=%d p=%g, C port of EnvSet.step + generatePerspectiveBatch + float32 "
+                      "concatenate (oracle/toric_oracle.c), one slice per thread, %.1f s; mean perspectives/env %.1f"
+                      % (n_envs, steps, a.d, a.p, dt, float(c[3]) / max(float(c[0]), 1.0)),
+            "seconds": dt, "steps": steps, "envs": n_envs}
+
+
+def run_reference(a):
+    """--impl reference: the CPU arm.  The reference is pure Python/numba and cannot travel to the GPU box,
+    so this times the oracle's C port of the same loop (kind "port") with every host core; each step
+    advances a bounded sample of --cpu-envs environments once."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import c_oracle as C
+    loop = C.ActorLoop(a.d, a.cpu_envs, a.p, seed=a.seed, nthreads=0)
+    loop.run(max(a.warmup, 1))
+    c0 = loop.counters.copy()
+    t0 = time.perf_counter()
+    loop.run(a.steps)
+    dt = time.perf_counter() - t0
+    c = loop.counters - c0
+    value = float(c[0]) / dt
+    sample = ("%d envs x %d steps, d=%d p=%g, C port of EnvSet.step + generatePerspectiveBatch + float32 concatenate "
+              "(oracle/toric_oracle.c), one slice per thread; mean perspectives/env %.1f"
+              % (a.cpu_envs, a.steps, a.d, a.p, float(c[3]) / max(float(c[0]), 1.0)))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+            "data": "synthetic", "config": {"workload": workload_name(a),
+                                            "note": "CPU arm: bounded sample of the same loop on the host cores"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": loop.nthreads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+def run_b200(a):
+    import numpy as np
+    import torch
+    import toric_rl_decoder_b200 as pkg
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    d, n = a.d, a.envs
+
+    eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p)   # envs shard by rank
+    eng.ensure_capacity(eng.worst_case_capacity())
+    eng.reset()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        eng.actor_pre()
+        eng.persp_write()
+    barrier()
+    eng.counters.zero_()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    evb = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]
+    evc = [torch.cuda.Event(enable_timing=True) for _ in range(a.steps)]
+    barrier()
+    with ClockSampler(local) as clk:
+        ev0.record()
+        for k in range(a.steps):
+            eng.actor_pre()            # actor_step_kernel + scan_blocks_kernel
+            evb[k].record()
+            eng.persp_write()          # persp_write_kernel
+            evc[k].record()
+        ev1.record()
+        barrier()
+    ms = ev0.elapsed_time(ev1)
+    write_ms = sum(b.elapsed_time(c) for b, c in zip(evb, evc)) / a.steps
+    ctr = eng.counters.clone()
+    assert int(eng.overflow.item()) == 0
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)           # time = max over ranks
+        dist.all_reduce(ctr, op=dist.ReduceOp.SUM)         # the path's only collective: counter all-reduce
+    ms = float(t.item())
+    c = {name: int(ctr[i].item()) for i, name in enumerate(pkg.engine.COUNTER_NAMES)}
+    total_steps = c["env_steps"]
+    assert total_steps == n * a.steps * world
+    value = total_steps / (ms * 1e-3)
+    sum_p_local = int(eng.counters[5].item())
+    p_bar = sum_p_local / float(n * a.steps)
+
+    peak, peak_src = load_peaks()
+    wbytes = write_kernel_bytes(d, n, sum_p_local / a.steps)
+    achieved = wbytes / (write_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "persp_write_kernel<%d>" % d, "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
+                "step_achieved": b_alg(d, n, sum_p_local / a.steps) / (ms / a.steps * 1e-3) / 1e9}
+    tr = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tr):
+        try:
+            roofline["traffic"] = json.load(open(tr)).get("persp_write_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- e2e: reference-facing call with HOST buffers (actions in, step results out) ----------
+    e2e = None
+    if not a.no_e2e:
+        e2e = run_e2e(a, eng, dev, dist, barrier, world)
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cpu = cpu_arm(a, a.cpu_seconds, a.cpu_envs)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u32 bit planes -> f32", "data": "synthetic",
+                "config": {"workload": workload_name(a), "d": d, "p_error": a.p, "envs_per_gpu": n,
+                           "global_envs": n * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
+                           "mean_perspectives_per_env": p_bar, "out_dtype": "float32",
+                           "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
+                                 % (wbytes / 1e9),
+                           "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps) / n},
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": 3 * a.steps,
+                "clocks": clk.summary(),
+                "counters": {k: c[k] for k in ("episodes", "solved", "ground_kept", "timeouts", "perspectives")}}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_e2e(a, eng, dev, dist, barrier, world):
+    """Same metric through the host-facing call: every step copies that step's actions (n,4) int32 from
+    pinned host memory, runs the fused actor step, and reads rewards, terminals, perspective counts and
+    the new states (uint8 n,2,d,d) back to pinned host memory.  The perspective tensor stays on the
+    device, where the reference also puts it (`.to(device)`, src/numba/util_actor.py:39)."""
+    import numpy as np
+    import torch
+    d, n = a.d, a.envs
+    rng = np.random.default_rng(a.seed + 17)
+    n_buf = 8
+    host_actions = []
+    for _ in range(n_buf):     # host policy: uniformly random qubit and Pauli (valid for any state)
+        arr = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)],
+                       axis=1).astype(np.int32)
+        host_actions.append(torch.from_numpy(arr).pin_memory())
+    h_reward = torch.empty(n, dtype=torch.float32).pin_memory()
+    h_term = torch.empty(n, dtype=torch.uint8).pin_memory()
+    h_counts = torch.empty(n, dtype=torch.int32).pin_memory()
+    h_state = torch.empty((n, 2, d, d), dtype=torch.uint8).pin_memory()
+    h2d = host_actions[0].numel() * 4
+    d2h = h_reward.numel() * 4 + h_term.numel() + h_counts.numel() * 4 + h_state.numel()
+
+    def one(k):
+        eng.actor_step(actions=host_actions[k % n_buf], auto_reset=True)
+        st = eng.get_state()
+        h_reward.copy_(eng.reward, non_blocking=True)
+        h_term.copy_(eng.terminal, non_blocking=True)
+        h_counts.copy_(eng.counts, non_blocking=True)
+        h_state.copy_(st, non_blocking=True)
+        torch.cuda.current_stream().synchronize()     # the caller consumes the results before the next step
+
+    for k in range(max(3, a.warmup)):
+        one(k)
+    barrier()
+    c0 = eng.counters.clone()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for k in range(a.steps):
+        one(k)
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    dc = eng.counters - c0
+    return {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "ms_per_step": ms / a.steps,
+            "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
+            "call": "ToricEngine.actor_step(host actions) + host read of reward/terminal/counts/states",
+            "policy": "host-supplied uniformly random qubit + Pauli"}
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)
+
+
+if __name__ == "__main__":
+    main()

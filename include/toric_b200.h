@@ -1,0 +1,127 @@
+/* toric_b200.h -- C ABI of libtoric_b200.so, the B200 (sm_100a) toric-code environment engine.
+ *
+ * Drop-in boundary for the env hot path of Lindeby/toric-RL-decoder.  The reference has no
+ * FFI of its own (it is pure Python); each entry point below names the reference interface it
+ * replaces (file:line relative to the reference checkout).  INTEGRATION.md shows the ctypes
+ * binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); all work is
+ *     enqueued asynchronously, the library never synchronises and never allocates or frees;
+ *   - d = lattice size, 3 <= d <= 32; n = number of environments;
+ *   - return value: 0 ok; -1 bad argument (d out of range, null pointer, n < 0);
+ *     -2 workspace / capacity too small; > 0 a cudaError_t from the launch.
+ *
+ * Device state layout (one lattice row per 32-bit word, bit j = column j):
+ *   qubits : uint32 [n][4][d]   bit planes x0, x1, z0, z1 of the Pauli codes
+ *                               (code 0:I 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3})
+ *   syn    : uint32 [n][2][d]   vertex plane V (= state[0]) and plaquette plane Pl (= state[1])
+ */
+#ifndef TORIC_B200_H
+#define TORIC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TC_ABI_VERSION 1
+#define TC_NUM_COUNTERS 16
+
+/* status bits written per env */
+#define TC_STATUS_BAD_ACTION 1
+#define TC_STATUS_RESET_GAVE_UP 2
+
+/* sampler modes of tc_reset / tc_actor_step */
+#define TC_SAMPLE_DEPOLARIZING 0 /* generateRandomError, ToricCode.py:130-151 */
+#define TC_SAMPLE_FIXED_WEIGHT 1 /* generateNRandomErrors, ToricCode.py:153-166 */
+#define TC_SAMPLE_FIXED_PLUS_P 2 /* generateNPlusQRandomErrors, results/small_p_error_test.py:43-52 */
+
+/* flags of tc_actor_step */
+#define TC_ACTOR_RANDOM_ACTIONS 1 /* draw the action on device (uniform over the perspective list x {X,Y,Z}) */
+#define TC_ACTOR_AUTO_RESET 2     /* reset envs that are terminal or past max_steps (Actor_mp.py:171-183) */
+
+int tc_abi_version(void);
+
+/* Bytes of scratch needed by tc_perspectives / tc_actor_step for n envs of size d. */
+int tc_workspace_bytes(int d, int64_t n, size_t* out_bytes);
+
+/* Mask injection / read-back: the reference injects error masks by assigning env.qubit_matrix and
+ * env.state (results/small_p_error_test.py:119-120).  codes: uint8 [n][2][d][d] Pauli codes. */
+int tc_pack_qubits(const uint8_t* codes, uint32_t* qubits, int d, int64_t n, void* stream);
+int tc_unpack_qubits(const uint32_t* qubits, uint8_t* codes, int d, int64_t n, void* stream);
+/* state01: uint8 [n][2][d][d] of 0/1 (any non-zero counts as a defect when packing). */
+int tc_pack_state(const uint8_t* state01, uint32_t* syn, int d, int64_t n, void* stream);
+int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, void* stream);
+
+/* createSyndromOpt (ToricCode.py:168-199): syn <- stencil(qubits). */
+int tc_syndrome(const uint32_t* qubits, uint32_t* syn, int d, int64_t n, void* stream);
+
+/* ToricCode.step + getReward + isTerminalState (ToricCode.py:62-88, :202-218), batched like
+ * EnvSet.step (src/EnvSet.py:38-47).  actions: int32 [n][4] = (matrix, row, col, op).  The syndrome
+ * is updated incrementally.  reward: float32 [n] (100 on terminal else defect difference);
+ * terminal: uint8 [n]; status: uint8 [n] (OR-ed with TC_STATUS_BAD_ACTION), nullable. */
+int tc_step(uint32_t* qubits, uint32_t* syn, const int32_t* actions, float* reward, uint8_t* terminal,
+            uint8_t* status, int d, int64_t n, void* stream);
+
+/* ToricCode.reset (ToricCode.py:90-127) for the envs listed in idx (int64 [n_idx], NULL = envs
+ * 0..n_idx-1), like EnvSet.resetAll / resetTerminalEnvs (src/EnvSet.py:19-36).  Sampling is
+ * Philox4x32-10 keyed by `seed` with counter (env_base + env, episode[env], draw); episode[env] is
+ * incremented.  p_thresh: uint32 [n] per-env error threshold floor(p * 2^32).  gs (sticky
+ * ground-state flag) is set to 1.  n_fixed = number of forced errors for the fixed-weight modes. */
+int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, const uint32_t* p_thresh,
+             uint32_t* episode, const int64_t* idx, int64_t n_idx, int mode, int n_fixed, uint64_t seed,
+             int64_t env_base, int d, void* stream);
+
+/* evalGroundState (ToricCode.py:289-337): gs[e] &= all four plane parities even. */
+int tc_ground_state(const uint32_t* qubits, uint8_t* gs, int d, int64_t n, void* stream);
+
+/* generatePerspectiveBatch + the concatenate / float32 layout of selectActionBatch
+ * (src/numba/util_actor.py:56-67 and :33-39; single-env forms src/util.py:46-150).
+ *   out      float32 [cap][2][d][d]  perspectives, env-major, per env all matrix-0 qubits row-major
+ *                                    then all matrix-1 qubits (rotated views)
+ *   pos      uint8   [cap][4]        (m, i, j, 0) per perspective                     (nullable)
+ *   counts   int32   [n]             perspectives per env
+ *   offsets  int64   [n+1]           exclusive prefix of counts; offsets[n] = total (= splice_idx)
+ * Envs whose perspectives would not fit in cap are skipped and *overflow (int32, nullable) is set.
+ * workspace: tc_workspace_bytes(d, n) bytes. */
+int tc_perspectives(const uint32_t* syn, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
+                    int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d,
+                    int64_t n, void* stream);
+
+/* The two halves of tc_perspectives, for callers that time or overlap them separately:
+ * count + scan (fills counts, offsets[n] and the workspace), then the streaming write. */
+int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void* workspace,
+                   size_t workspace_bytes, int d, int64_t n, void* stream);
+int tc_persp_write(const uint32_t* syn, float* out, uint8_t* pos, int64_t* offsets, int32_t* overflow,
+                   int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n, void* stream);
+
+/* One fused actor iteration over all envs (the loop body of src/Actor_mp.py:104-185 minus the
+ * network): optional on-device random action, step, reward/terminal, episode bookkeeping with
+ * auto-reset, then the perspectives of the resulting states.
+ *   actions     int32 [n][4]  read (host policy) or written (TC_ACTOR_RANDOM_ACTIONS)
+ *   steps       int32 [n]     steps taken in the current episode
+ *   counters    int64 [TC_NUM_COUNTERS] running totals, nullable
+ *   prev_syn    uint32 [n][2][d] copy of the pre-reset post-step syndrome (transition next_state), nullable
+ */
+int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
+                  uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,
+                  const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode,
+                  int n_fixed, uint64_t seed, int64_t env_base, float* out, uint8_t* pos, int32_t* counts,
+                  int64_t* offsets, int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes,
+                  int d, int64_t n, void* stream);
+
+/* tc_actor_step without the perspective write (follow with tc_persp_write on the same workspace). */
+int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
+                 uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,
+                 const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
+                 uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
+                 size_t workspace_bytes, int d, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TORIC_B200_H */

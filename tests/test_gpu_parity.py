@@ -1,0 +1,203 @@
+"""GPU parity: libtoric_b200.so (through the C ABI / the host mirror) against the golden fixtures
+generated from the reference and against the numpy oracle on seeded inputs.  Bit-exact everywhere."""
+import numpy as np
+import pytest
+import torch
+
+import golden
+from oracle import toric_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pkg(cuda_device):
+    import toric_rl_decoder_b200 as pkg
+    from toric_rl_decoder_b200 import _lib
+    _lib.load()
+    return pkg
+
+
+def _views(eng, n=None):
+    persp, pos, counts, offsets = eng.perspective_views(n)
+    return (persp.cpu().numpy(), pos.cpu().numpy()[:, :3].astype(np.int64), counts.cpu().numpy().astype(np.int64),
+            offsets.cpu().numpy())
+
+
+@pytest.mark.parametrize("d", golden.ALL_D)
+def test_inject_syndrome_logical(pkg, d):
+    g = golden.per_d(d)
+    k = len(g["qubits"])
+    eng = pkg.ToricEngine(d, k)
+    eng.set_qubits(g["qubits"])
+    assert (eng.get_qubits().cpu().numpy() == g["qubits"]).all()          # pack/unpack round trip
+    assert (eng.get_state().cpu().numpy() == g["state"]).all()            # createSyndromOpt
+    assert (eng.ground_state().cpu().numpy().astype(bool) == g["gs"]).all()  # evalGroundState
+
+
+@pytest.mark.parametrize("d", golden.ALL_D)
+def test_perspectives_golden(pkg, d):
+    g = golden.per_d(d)
+    k = len(g["state"])
+    eng = pkg.ToricEngine(d, k)
+    for states, counts, pos, views in ((g["state"], g["counts"], g["positions"], g["views"]),
+                                       (g["step_state"][:, -1], g["counts_last"], g["positions_last"],
+                                        g["views_last"])):
+        eng.set_state(states)
+        eng.perspectives()
+        p, ps, c, off = _views(eng)
+        assert (c == counts).all()
+        assert off[0] == 0 and (off[1:] == np.cumsum(counts)).all()
+        assert (ps == pos).all()
+        assert p.dtype == np.float32 and p.shape == views.shape
+        assert (p == views.astype(np.float32)).all()
+
+
+@pytest.mark.parametrize("d", (3, 5))
+def test_exhaustive_masks(pkg, d):
+    g = golden.exhaustive(d)
+    k = len(g["qubits"])
+    eng = pkg.ToricEngine(d, k)
+    eng.set_qubits(g["qubits"])
+    assert (eng.get_state().cpu().numpy() == g["state"]).all()
+    assert (eng.ground_state().cpu().numpy().astype(bool) == g["gs"]).all()
+    eng.perspectives()
+    p, ps, c, off = _views(eng)
+    assert (c == g["counts"]).all() and (ps == g["positions"]).all()
+    assert (p == g["views"].astype(np.float32)).all()
+
+
+@pytest.mark.parametrize("d", golden.ALL_D)
+def test_step_sequences_golden(pkg, d):
+    g = golden.per_d(d)
+    k, T = g["actions"].shape[:2]
+    eng = pkg.ToricEngine(d, k)
+    eng.set_qubits(g["qubits"])
+    for t in range(T):
+        reward, terminal = eng.step(torch.from_numpy(g["actions"][:, t].astype(np.int64)))
+        assert (eng.get_qubits().cpu().numpy() == g["step_qubits"][:, t]).all()
+        assert (eng.get_state().cpu().numpy() == g["step_state"][:, t]).all()     # incremental == full recompute
+        assert (reward.cpu().numpy().astype(np.float64) == g["step_reward"][:, t]).all()
+        assert (terminal.cpu().numpy().astype(bool) == g["step_terminal"][:, t]).all()
+        assert (eng.ground_state().cpu().numpy().astype(bool) == g["step_gs"][:, t]).all()   # sticky
+    assert int(eng.status.max().item()) == 0
+
+
+def test_envset_mirror_golden(pkg):
+    """EnvSetB200 behaves like src/EnvSet.py on the reference's own recorded run (dtypes included)."""
+    g = golden.batch_d7()
+    n = len(g["qubits0"])
+    es = pkg.EnvSetB200({"size": 7, "p_error": 0.1}, n)
+    assert es.size == 7 and es.no_envs == n
+    es.engine.set_qubits(g["qubits0"])
+    for t in range(g["actions"].shape[0]):
+        st, rw, tm, info = es.step(g["actions"][t])
+        assert st.dtype == np.int64 and rw.dtype == np.float64 and tm.dtype == np.bool_ and info == {}
+        assert (st == g["states"][t]).all() and (rw == g["rewards"][t]).all() and (tm == g["terminals"][t]).all()
+    persp, pos, counts, offsets = pkg.generatePerspectiveBatch(3, 7, st)
+    assert persp.dtype == torch.float32 and persp.is_cuda
+    assert (offsets.cpu().numpy()[1:] == g["splice_idx"]).all()
+    assert (pos.cpu().numpy() == g["positions"]).all()
+    assert (persp.cpu().numpy() == g["views"].astype(np.float32)).all()
+
+
+def test_single_env_api(pkg):
+    """ToricCodeB200 mirrors gym_ToricCode's ToricCode, injected with a golden mask."""
+    g = golden.per_d(5)
+    env = pkg.ToricCodeB200({"size": 5, "min_qbit_errors": 0, "p_error": 0.1})
+    assert env.system_size == 5 and int(env.action_space.high[-1]) == 3
+    e = 1
+    env.qubit_matrix = g["qubits"][e]
+    assert (env.state == g["state"][e]).all() and env.state.dtype == np.int64
+    assert (env.createSyndromOpt(g["qubits"][e]) == g["state"][e]).all()
+    for t in range(g["actions"].shape[1]):
+        st, r, term, info = env.step(list(g["actions"][e, t]))
+        assert (st == g["step_state"][e, t]).all() and r == g["step_reward"][e, t]
+        assert term == bool(g["step_terminal"][e, t]) and env.isTerminalState(st) == term
+        assert env.evalGroundState() == bool(g["step_gs"][e, t])
+    views, pos = pkg.generatePerspectiveOptimized(2, 5, g["state"][e].astype(np.int64))
+    ov, op = O.perspectives(g["state"][e].astype(np.int64))
+    assert len(views) == len(ov) and all((a == b).all() for a, b in zip(views, ov))
+    assert pos == [tuple(int(x) for x in p) for p in op]
+    pl = pkg.generatePerspective(2, 5, g["state"][e].astype(np.int64))
+    assert all((a.perspective == b).all() and a.position == tuple(c) for a, b, c in zip(pl, ov, op))
+    s = env.reset(p_error=0.2)
+    assert s.shape == (2, 5, 5) and s.any() and env.ground_state is True
+    assert (O.syndrome(env.qubit_matrix) == s).all()
+
+
+@pytest.mark.parametrize("d,n", ((7, 1024), (9, 256), (4, 64), (16, 64), (17, 32), (32, 8)))
+def test_seeded_random_vs_oracle(pkg, d, n):
+    """Seeded masks and action sequences at sizes the oracle finishes in seconds."""
+    rng = np.random.default_rng(100 + d)
+    q = (rng.random((n, 2, d, d)) < 0.08) * rng.integers(1, 4, (n, 2, d, d))
+    q = q.astype(np.uint8)
+    q[0] = 0                                   # empty env: no perspectives, terminal syndrome
+    q[1] = rng.integers(0, 4, (2, d, d))       # dense env
+    eng = pkg.ToricEngine(d, n)
+    eng.set_qubits(q)
+    s = O.syndrome(q)
+    assert (eng.get_state().cpu().numpy() == s).all()
+    qq = q.astype(np.int64)
+    T = 4
+    for t in range(T):
+        acts = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(0, 4, n)], 1)
+        reward, terminal = eng.step(torch.from_numpy(acts))
+        rw, tm = reward.cpu().numpy(), terminal.cpu().numpy()
+        for e in range(n):
+            qq[e], ns, r, term = O.step(qq[e], s[e], acts[e])
+            s[e] = ns
+            assert rw[e] == r and bool(tm[e]) == term
+        assert (eng.get_state().cpu().numpy() == s).all()
+        assert (eng.get_qubits().cpu().numpy() == qq).all()
+    eng.perspectives()
+    p, ps, c, off = _views(eng)
+    op, opos, oc, ooff = O.perspectives_batch(s)
+    assert (c == oc).all() and (off == ooff).all() and (ps == opos).all()
+    assert (p == op).all()
+
+
+def test_bad_actions_are_masked(pkg):
+    d, n = 5, 8
+    eng = pkg.ToricEngine(d, n)
+    q = np.zeros((n, 2, d, d), np.uint8)
+    q[:, 0, 1, 1] = 1
+    eng.set_qubits(q)
+    acts = np.array([[2, 0, 0, 1], [0, 5, 0, 1], [0, 0, -1, 1], [0, 0, 0, 4], [0, 0, 0, 0], [1, 4, 4, 3],
+                     [0, 1, 1, 1], [-1, 0, 0, 1]])
+    reward, terminal = eng.step(torch.from_numpy(acts))
+    st = eng.status.cpu().numpy()
+    assert list(st) == [1, 1, 1, 1, 0, 0, 0, 1]
+    after = eng.get_qubits().cpu().numpy()
+    for e in (0, 1, 2, 3, 4, 7):
+        assert (after[e] == q[e]).all() and reward[e].item() == 0.0
+    assert terminal[6].item() == 1 and reward[6].item() == 100.0
+
+
+def test_capacity_overflow_regenerates(pkg):
+    d, n = 7, 64
+    rng = np.random.default_rng(5)
+    q = ((rng.random((n, 2, d, d)) < 0.1) * rng.integers(1, 4, (n, 2, d, d))).astype(np.uint8)
+    eng = pkg.ToricEngine(d, n)
+    eng.set_qubits(q)
+    eng.ensure_capacity(10)      # far too small on purpose
+    eng.perspectives()
+    p, ps, c, off = _views(eng)
+    op, opos, oc, ooff = O.perspectives_batch(O.syndrome(q))
+    assert (c == oc).all() and (p == op).all() and (ps == opos).all()
+
+
+def test_abi_argument_errors(pkg):
+    from toric_rl_decoder_b200 import _lib
+    lib = _lib.load()
+    assert lib.tc_syndrome(None, None, 7, 4, None) == -1
+    assert lib.tc_syndrome(None, None, 2, 4, None) == -1
+    assert lib.tc_syndrome(None, None, 33, 4, None) == -1
+    eng = pkg.ToricEngine(7, 4)
+    small = torch.zeros(8, dtype=torch.uint8, device="cuda")
+    eng.ensure_capacity(16)
+    rc = lib.tc_perspectives(eng.syn.data_ptr(), eng.out.data_ptr(), eng.pos.data_ptr(), eng.counts.data_ptr(),
+                             eng.offsets.data_ptr(), eng.overflow.data_ptr(), eng.cap, small.data_ptr(), 8, 7, 4, None)
+    assert rc == -2
+    with pytest.raises(ValueError):
+        pkg.ToricEngine(2, 4)

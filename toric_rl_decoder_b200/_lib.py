@@ -1,0 +1,65 @@
+"""ctypes binding of libtoric_b200.so (the C ABI declared in include/toric_b200.h).
+
+There is no CPU fallback: if the library is missing this raises, and every entry point needs
+device pointers.
+"""
+import ctypes
+import os
+
+from .buildlib import LIB_PATH
+
+_c = ctypes
+_vp, _i, _i64, _u64, _sz = _c.c_void_p, _c.c_int, _c.c_int64, _c.c_uint64, _c.c_size_t
+
+# name -> argtypes, exactly the prototypes of include/toric_b200.h
+SIGNATURES = {
+    "tc_abi_version": [],
+    "tc_workspace_bytes": [_i, _i64, _c.POINTER(_sz)],
+    "tc_pack_qubits": [_vp, _vp, _i, _i64, _vp],
+    "tc_unpack_qubits": [_vp, _vp, _i, _i64, _vp],
+    "tc_pack_state": [_vp, _vp, _i, _i64, _vp],
+    "tc_unpack_state": [_vp, _vp, _i, _i64, _vp],
+    "tc_syndrome": [_vp, _vp, _i, _i64, _vp],
+    "tc_step": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _vp],
+    "tc_reset": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _u64, _i64, _i, _vp],
+    "tc_ground_state": [_vp, _vp, _i, _i64, _vp],
+    "tc_perspectives": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_persp_count": [_vp, _vp, _vp, _vp, _sz, _i, _i64, _vp],
+    "tc_persp_write": [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_actor_pre": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
+                     _vp, _vp, _vp, _sz, _i, _i64, _vp],
+    "tc_actor_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
+                      _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "libtoric_b200.so is not built (%s). Run `python -m toric_rl_decoder_b200.buildlib` or "
+            "`__graft_entry__.build()`. There is no CPU fallback." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)      # AttributeError if the symbol is missing
+        fn.argtypes = argtypes
+        fn.restype = _i
+    if lib.tc_abi_version() != 1:
+        raise RuntimeError("libtoric_b200.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc == 0:
+        return
+    if rc == -1:
+        raise ValueError("%s: bad argument" % what)
+    if rc == -2:
+        raise ValueError("%s: workspace or capacity too small" % what)
+    raise RuntimeError("%s: CUDA error %d" % (what, rc))

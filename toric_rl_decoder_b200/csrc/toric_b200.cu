@@ -1,0 +1,579 @@
+// libtoric_b200.so -- kernels and C ABI (include/toric_b200.h) of the toric-code environment engine.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include "../../include/toric_b200.h"
+
+#include "common.cuh"
+#include "persp_write.cuh"
+#include "state_kernels.cuh"
+
+namespace tc {
+
+// ------------------------------------------------------------------------------------------------
+// mask injection / read-back
+// ------------------------------------------------------------------------------------------------
+// one thread per (env, matrix, row)
+__global__ void pack_qubits_kernel(const uint8_t* __restrict__ codes, uint32_t* __restrict__ qubits, int d,
+                                   int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 2 * d) return;
+  const int64_t e = t / (2 * d);
+  const int mr = (int)(t - e * 2 * d);
+  const int m = mr / d, i = mr - m * d;
+  const uint8_t* src = codes + t * d;
+  uint32_t x = 0, z = 0;
+  for (int j = 0; j < d; ++j) {
+    const uint32_t c = src[j] & 3u;
+    x |= (uint32_t)(c == 1u || c == 2u) << j;
+    z |= (uint32_t)(c >= 2u) << j;
+  }
+  qubits[(e * 4 + m) * d + i] = x;
+  qubits[(e * 4 + 2 + m) * d + i] = z;
+}
+
+__global__ void unpack_qubits_kernel(const uint32_t* __restrict__ qubits, uint8_t* __restrict__ codes, int d,
+                                     int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 2 * d) return;
+  const int64_t e = t / (2 * d);
+  const int mr = (int)(t - e * 2 * d);
+  const int m = mr / d, i = mr - m * d;
+  const uint32_t x = qubits[(e * 4 + m) * d + i], z = qubits[(e * 4 + 2 + m) * d + i];
+  uint8_t* dst = codes + t * d;
+  for (int j = 0; j < d; ++j) {
+    const uint32_t xb = (x >> j) & 1u, zb = (z >> j) & 1u;
+    dst[j] = (uint8_t)(xb ? (zb ? 2 : 1) : (zb ? 3 : 0));
+  }
+}
+
+// one thread per (env, plane, row)
+__global__ void pack_state_kernel(const uint8_t* __restrict__ st, uint32_t* __restrict__ syn, int d, int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 2 * d) return;
+  const uint8_t* src = st + t * d;
+  uint32_t w = 0;
+  for (int j = 0; j < d; ++j) w |= (uint32_t)(src[j] != 0) << j;
+  syn[t] = w;
+}
+
+__global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 2 * d) return;
+  const uint32_t w = syn[t];
+  uint8_t* dst = st + t * d;
+  for (int j = 0; j < d; ++j) dst[j] = (uint8_t)((w >> j) & 1u);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2 syndrome, K3 step, K1 reset, K5 ground state (standalone forms)
+// ------------------------------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(kThreads) syndrome_kernel(const uint32_t* __restrict__ qubits,
+                                                            uint32_t* __restrict__ syn, int d, int64_t n) {
+  const uint32_t gmask = group_mask<G>();
+  const int r = threadIdx.x & (G - 1);
+  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  const bool valid = e < n;
+  if (!valid) e = n - 1;
+  Rows s;
+  load_qubits<G>(qubits, e, d, r, s);
+  syndrome_rows<G>(gmask, d, r, s);
+  if (valid) store_syn<G>(syn, e, d, r, s);
+}
+
+template <int G>
+__global__ void __launch_bounds__(kThreads)
+step_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, const int32_t* __restrict__ actions,
+            float* __restrict__ reward, uint8_t* __restrict__ terminal, uint8_t* __restrict__ status, int d,
+            int64_t n) {
+  const uint32_t gmask = group_mask<G>();
+  const int r = threadIdx.x & (G - 1);
+  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  const bool valid = e < n;
+  if (!valid) e = n - 1;
+  Rows s;
+  load_qubits<G>(qubits, e, d, r, s);
+  load_syn<G>(syn, e, d, r, s);
+  const int4 a = *reinterpret_cast<const int4*>(actions + e * 4);
+  const int before = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
+  const bool ok = apply_action<G>(d, r, a.x, a.y, a.z, a.w, s);
+  const int after = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
+  if (!valid) return;
+  store_qubits<G>(qubits, e, d, r, s);
+  store_syn<G>(syn, e, d, r, s);
+  if (r == 0) {
+    // getReward / isTerminalState (ToricCode.py:202-218)
+    reward[e] = after == 0 ? 100.0f : (float)(before - after);
+    terminal[e] = after == 0 ? 1 : 0;
+    if (status && !ok) status[e] |= kStatusBadAction;
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(kThreads)
+reset_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint8_t* __restrict__ gs,
+             uint8_t* __restrict__ status, const uint32_t* __restrict__ p_thresh, uint32_t* __restrict__ episode,
+             const int64_t* __restrict__ idx, int64_t n_idx, int mode, int n_fixed, uint2 key, int64_t env_base,
+             int d) {
+  const uint32_t gmask = group_mask<G>();
+  const int r = threadIdx.x & (G - 1);
+  const int64_t k = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  if (k >= n_idx) return;   // whole groups leave together
+  const int64_t e = idx ? idx[k] : k;
+  const uint32_t ep = episode[e];
+  Rows s;
+  uint8_t st = 0;
+  SampleStats stats;
+  sample_errors<G>(gmask, d, r, (uint64_t)(env_base + e), ep, p_thresh[e], mode, n_fixed, key, s, st, stats);
+  store_qubits<G>(qubits, e, d, r, s);
+  store_syn<G>(syn, e, d, r, s);
+  __syncwarp(gmask);
+  if (r == 0) {
+    episode[e] = ep + 1;
+    if (gs) gs[e] = 1;
+    if (status && st) status[e] |= st;
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(kThreads) ground_state_kernel(const uint32_t* __restrict__ qubits,
+                                                                uint8_t* __restrict__ gs, int d, int64_t n) {
+  const uint32_t gmask = group_mask<G>();
+  const int r = threadIdx.x & (G - 1);
+  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  const bool valid = e < n;
+  if (!valid) e = n - 1;
+  Rows s;
+  load_qubits<G>(qubits, e, d, r, s);
+  const bool even = parity_even<G>(gmask, s);
+  if (valid && r == 0 && !even) gs[e] = 0;   // sticky (ToricCode.py:332-335)
+}
+
+// ------------------------------------------------------------------------------------------------
+// perspective count + CTA-local exclusive prefix  (first half of K4)
+// ------------------------------------------------------------------------------------------------
+template <int G>
+__device__ __forceinline__ void cta_count_prefix(int count, bool valid, int r, int64_t e,
+                                                 int32_t* __restrict__ counts, int32_t* __restrict__ local_off,
+                                                 int32_t* __restrict__ block_sum) {
+  constexpr int EPB = kThreads / G;
+  __shared__ int sc[32];
+  const int ge = threadIdx.x / G;
+  if (r == 0) sc[ge] = valid ? count : 0;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    const int v = lane < EPB ? sc[lane] : 0;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane < EPB) sc[lane] = inc - v;
+    if (lane == 31) block_sum[blockIdx.x] = inc;
+  }
+  __syncthreads();
+  if (valid && r == 0) {
+    counts[e] = count;
+    local_off[e] = sc[ge];
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(kThreads)
+persp_count_kernel(const uint32_t* __restrict__ syn, int32_t* __restrict__ counts, int32_t* __restrict__ local_off,
+                   int32_t* __restrict__ block_sum, int d, int64_t n) {
+  const uint32_t gmask = group_mask<G>();
+  const int r = threadIdx.x & (G - 1);
+  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  const bool valid = e < n;
+  if (!valid) e = n - 1;
+  Rows s;
+  load_syn<G>(syn, e, d, r, s);
+  uint32_t m0, m1;
+  persp_masks<G>(gmask, d, r, s.v, s.pl, m0, m1);
+  const int count = gsum<G>(gmask, __popc(m0) + __popc(m1));
+  cta_count_prefix<G>(count, valid, r, e, counts, local_off, block_sum);
+}
+
+// single CTA: exclusive scan of the per-CTA sums -> block_off (int64), grand total -> offsets[n]
+__global__ void __launch_bounds__(1024)
+scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ block_off, int64_t nblocks,
+                   int64_t* __restrict__ total_out, int64_t* __restrict__ counters) {
+  __shared__ long long warp_tot[32];
+  __shared__ long long carry_s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < nblocks; base += 1024) {
+    const int64_t i = base + tid;
+    const long long v = i < nblocks ? (long long)block_sum[i] : 0;
+    long long inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const long long t = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      const long long w = warp_tot[lane];
+      long long winc = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const long long t = __shfl_up_sync(0xffffffffu, winc, o);
+        if (lane >= o) winc += t;
+      }
+      warp_tot[lane] = winc - w;   // exclusive prefix of the warp totals
+    }
+    __syncthreads();
+    const long long carry = carry_s;
+    if (i < nblocks) block_off[i] = carry + warp_tot[warp] + (inc - v);
+    __syncthreads();
+    if (tid == 1023) carry_s = carry + warp_tot[31] + inc;   // last thread's inclusive value closes the tile
+    __syncthreads();
+  }
+  if (tid == 0) {
+    *total_out = carry_s;
+    if (counters) atomicAdd(reinterpret_cast<unsigned long long*>(counters + kCtrPerspectives),
+                            (unsigned long long)carry_s);
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// fused actor iteration: [random action] -> step -> reward/terminal -> bookkeeping / auto-reset -> count
+// (loop body of src/Actor_mp.py:104-185 without the network; perspectives follow in persp_write_kernel)
+// ------------------------------------------------------------------------------------------------
+struct ActorArgs {
+  uint32_t* qubits;
+  uint32_t* syn;
+  uint32_t* prev_syn;
+  int32_t* actions;
+  float* reward;
+  uint8_t* terminal;
+  uint8_t* gs;
+  uint8_t* status;
+  int32_t* steps;
+  uint32_t* episode;
+  const uint32_t* p_thresh;
+  int64_t* counters;
+  int32_t* counts;
+  int32_t* local_off;
+  int32_t* block_sum;
+  uint2 key;
+  int64_t env_base;
+  int64_t n;
+  int flags, max_steps, mode, n_fixed, d;
+};
+
+template <int G>
+__global__ void __launch_bounds__(kThreads) actor_step_kernel(const ActorArgs a) {
+  __shared__ unsigned int s_ctr[kNumCounters];
+  if (threadIdx.x < kNumCounters) s_ctr[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t gmask = group_mask<G>();
+  const int d = a.d;
+  const int r = threadIdx.x & (G - 1);
+  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  const bool valid = e < a.n;
+  if (!valid) e = a.n - 1;
+  const bool lead = valid && r == 0;
+  Rows s;
+  load_qubits<G>(a.qubits, e, d, r, s);
+  load_syn<G>(a.syn, e, d, r, s);
+  uint32_t ep = a.episode[e];
+  int stp = a.steps[e];
+  const uint64_t env_id = (uint64_t)(a.env_base + e);
+
+  int am, ai, aj, aop;
+  if (a.flags & TC_ACTOR_RANDOM_ACTIONS) {
+    uint32_t m0, m1;
+    persp_masks<G>(gmask, d, r, s.v, s.pl, m0, m1);
+    random_action<G>(gmask, d, r, m0, m1, env_id, ep, (uint32_t)stp, a.key, am, ai, aj, aop);
+    if (lead) *reinterpret_cast<int4*>(a.actions + e * 4) = make_int4(am, ai, aj, aop);
+  } else {
+    const int4 act = *reinterpret_cast<const int4*>(a.actions + e * 4);
+    am = act.x; ai = act.y; aj = act.z; aop = act.w;
+  }
+  const int before = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
+  const bool ok = apply_action<G>(d, r, am, ai, aj, aop, s);
+  const int after = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
+  const bool term = after == 0;
+  const bool even = parity_even<G>(gmask, s);
+  stp += 1;
+  if (lead) {
+    a.reward[e] = term ? 100.0f : (float)(before - after);
+    a.terminal[e] = term ? 1 : 0;
+    a.gs[e] = even ? 1 : 0;
+    atomicAdd(&s_ctr[kCtrEnvSteps], 1u);
+    if (!ok) {
+      if (a.status) a.status[e] |= kStatusBadAction;
+      atomicAdd(&s_ctr[kCtrBadActions], 1u);
+    }
+  }
+  if (a.prev_syn && valid) store_syn<G>(a.prev_syn, e, d, r, s);
+
+  const bool done = term || stp > a.max_steps;      // Actor_mp.py:171-172
+  if ((a.flags & TC_ACTOR_AUTO_RESET) && done) {     // uniform inside the group
+    uint8_t st = 0;
+    SampleStats stats;
+    sample_errors<G>(gmask, d, r, env_id, ep, a.p_thresh[e], a.mode, a.n_fixed, a.key, s, st, stats);
+    const int nx = gsum<G>(gmask, stats.nx), ny = gsum<G>(gmask, stats.ny), nz = gsum<G>(gmask, stats.nz);
+    ep += 1;
+    stp = 0;
+    if (lead) {
+      atomicAdd(&s_ctr[kCtrEpisodes], 1u);
+      if (term) atomicAdd(&s_ctr[kCtrSolved], 1u); else atomicAdd(&s_ctr[kCtrTimeouts], 1u);
+      if (term && even) atomicAdd(&s_ctr[kCtrGroundKept], 1u);
+      atomicAdd(&s_ctr[kCtrErrX], (unsigned)nx);
+      atomicAdd(&s_ctr[kCtrErrY], (unsigned)ny);
+      atomicAdd(&s_ctr[kCtrErrZ], (unsigned)nz);
+      atomicAdd(&s_ctr[kCtrQubitsSampled], (unsigned)(2 * d * d));
+      atomicAdd(&s_ctr[kCtrResetAttempts], (unsigned)stats.attempts);
+      if (st && a.status) a.status[e] |= st;
+    }
+  }
+  if (valid) {
+    store_qubits<G>(a.qubits, e, d, r, s);
+    store_syn<G>(a.syn, e, d, r, s);
+  }
+  if (lead) {
+    a.steps[e] = stp;
+    a.episode[e] = ep;
+  }
+  uint32_t m0, m1;
+  persp_masks<G>(gmask, d, r, s.v, s.pl, m0, m1);
+  const int count = gsum<G>(gmask, __popc(m0) + __popc(m1));
+  cta_count_prefix<G>(count, valid, r, e, a.counts, a.local_off, a.block_sum);   // has __syncthreads
+  if (a.counters && threadIdx.x < kNumCounters && s_ctr[threadIdx.x])
+    atomicAdd(reinterpret_cast<unsigned long long*>(a.counters + threadIdx.x), (unsigned long long)s_ctr[threadIdx.x]);
+}
+
+}  // namespace tc
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+namespace {
+
+using namespace tc;
+
+inline bool bad_d(int d) { return d < kMinD || d > kMaxD; }
+inline int launch_status() {
+  const cudaError_t err = cudaGetLastError();
+  return err == cudaSuccess ? 0 : (int)err;
+}
+inline unsigned grid_for(int64_t threads, int per_block) { return (unsigned)((threads + per_block - 1) / per_block); }
+inline uint2 make_key(uint64_t seed) { return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)); }
+
+#define TC_DISPATCH_G(d, CALL)                 \
+  do {                                         \
+    if ((d) <= 8) { constexpr int G = 8; CALL; }        \
+    else if ((d) <= 16) { constexpr int G = 16; CALL; } \
+    else { constexpr int G = 32; CALL; }                \
+  } while (0)
+
+struct Workspace {
+  int32_t* local_off;
+  int32_t* block_sum;
+  int64_t* block_off;
+  int64_t nblocks;
+  int epb;
+  size_t bytes;
+};
+
+inline Workspace carve(void* ws, int d, int64_t n) {
+  Workspace w;
+  w.epb = kThreads / group_size_for(d);
+  w.nblocks = (n + w.epb - 1) / w.epb;
+  size_t o = 0;
+  char* base = static_cast<char*>(ws);
+  w.local_off = reinterpret_cast<int32_t*>(base + o);
+  o += (size_t)n * 4;
+  w.block_sum = reinterpret_cast<int32_t*>(base + o);
+  o += (size_t)w.nblocks * 4;
+  o = (o + 15) & ~(size_t)15;
+  w.block_off = reinterpret_cast<int64_t*>(base + o);
+  o += (size_t)w.nblocks * 8;
+  w.bytes = (o + 255) & ~(size_t)255;
+  return w;
+}
+
+template <int D>
+void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
+                  int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
+  constexpr int WPB = PerspCfg<D>::kWarps;
+  persp_write_kernel<D><<<grid_for(n, WPB), WPB * 32, 0, st>>>(syn, w.local_off, w.block_off, w.epb, out, pos,
+                                                               offsets, overflow, cap, n);
+}
+
+int write_dispatch(int d, const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
+                   int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
+  switch (d) {
+#define TC_CASE(D) case D: launch_write<D>(syn, w, out, pos, offsets, overflow, cap, n, st); break;
+    TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8) TC_CASE(9) TC_CASE(10)
+    TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16) TC_CASE(17) TC_CASE(18)
+    TC_CASE(19) TC_CASE(20) TC_CASE(21) TC_CASE(22) TC_CASE(23) TC_CASE(24) TC_CASE(25) TC_CASE(26)
+    TC_CASE(27) TC_CASE(28) TC_CASE(29) TC_CASE(30) TC_CASE(31) TC_CASE(32)
+#undef TC_CASE
+    default: return -1;
+  }
+  return launch_status();
+}
+
+}  // namespace
+
+extern "C" {
+
+int tc_abi_version(void) { return TC_ABI_VERSION; }
+
+int tc_workspace_bytes(int d, int64_t n, size_t* out_bytes) {
+  if (bad_d(d) || n < 0 || !out_bytes) return -1;
+  *out_bytes = carve(nullptr, d, n).bytes;
+  return 0;
+}
+
+int tc_pack_qubits(const uint8_t* codes, uint32_t* qubits, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !codes || !qubits) return -1;
+  if (n == 0) return 0;
+  pack_qubits_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(codes, qubits, d, n);
+  return launch_status();
+}
+
+int tc_unpack_qubits(const uint32_t* qubits, uint8_t* codes, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !codes || !qubits) return -1;
+  if (n == 0) return 0;
+  unpack_qubits_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(qubits, codes, d, n);
+  return launch_status();
+}
+
+int tc_pack_state(const uint8_t* state01, uint32_t* syn, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
+  if (n == 0) return 0;
+  pack_state_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(state01, syn, d, n);
+  return launch_status();
+}
+
+int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
+  if (n == 0) return 0;
+  unpack_state_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, n);
+  return launch_status();
+}
+
+int tc_syndrome(const uint32_t* qubits, uint32_t* syn, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !qubits || !syn) return -1;
+  if (n == 0) return 0;
+  TC_DISPATCH_G(d, (syndrome_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                       qubits, syn, d, n)));
+  return launch_status();
+}
+
+int tc_step(uint32_t* qubits, uint32_t* syn, const int32_t* actions, float* reward, uint8_t* terminal,
+            uint8_t* status, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !qubits || !syn || !actions || !reward || !terminal) return -1;
+  if ((uintptr_t)actions & 15) return -1;
+  if (n == 0) return 0;
+  TC_DISPATCH_G(d, (step_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                       qubits, syn, actions, reward, terminal, status, d, n)));
+  return launch_status();
+}
+
+int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, const uint32_t* p_thresh,
+             uint32_t* episode, const int64_t* idx, int64_t n_idx, int mode, int n_fixed, uint64_t seed,
+             int64_t env_base, int d, void* stream) {
+  if (bad_d(d) || n_idx < 0 || !qubits || !syn || !p_thresh || !episode) return -1;
+  if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
+  if (n_idx == 0) return 0;
+  TC_DISPATCH_G(d, (reset_kernel<G><<<grid_for(n_idx * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                       qubits, syn, gs, status, p_thresh, episode, idx, n_idx, mode, n_fixed, make_key(seed),
+                       env_base, d)));
+  return launch_status();
+}
+
+int tc_ground_state(const uint32_t* qubits, uint8_t* gs, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !qubits || !gs) return -1;
+  if (n == 0) return 0;
+  TC_DISPATCH_G(d, (ground_state_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                       qubits, gs, d, n)));
+  return launch_status();
+}
+
+int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void* workspace,
+                   size_t workspace_bytes, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !syn || !counts || !offsets || !workspace) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+    return launch_status();
+  }
+  TC_DISPATCH_G(d, (persp_count_kernel<G><<<(unsigned)w.nblocks, kThreads, 0, st>>>(syn, counts, w.local_off,
+                                                                                    w.block_sum, d, n)));
+  scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, nullptr);
+  return launch_status();
+}
+
+int tc_persp_write(const uint32_t* syn, float* out, uint8_t* pos, int64_t* offsets, int32_t* overflow,
+                   int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || cap < 0 || !syn || !offsets || !workspace) return -1;
+  if (cap > 0 && !out) return -1;
+  if (((uintptr_t)out & 15) || ((uintptr_t)pos & 3)) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
+  if (n == 0) return 0;
+  return write_dispatch(d, syn, w, out, pos, offsets, overflow, cap, n, (cudaStream_t)stream);
+}
+
+int tc_perspectives(const uint32_t* syn, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
+                    int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
+                    void* stream) {
+  const int rc = tc_persp_count(syn, counts, offsets, workspace, workspace_bytes, d, n, stream);
+  if (rc != 0) return rc;
+  return tc_persp_write(syn, out, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n, stream);
+}
+
+int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
+                 uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,
+                 const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
+                 uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
+                 size_t workspace_bytes, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode ||
+      !p_thresh || !counts || !offsets || !workspace)
+    return -1;
+  if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
+  if ((uintptr_t)actions & 15) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+    return launch_status();
+  }
+  ActorArgs a;
+  a.qubits = qubits; a.syn = syn; a.prev_syn = prev_syn; a.actions = actions; a.reward = reward;
+  a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
+  a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
+  a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
+  a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d;
+  TC_DISPATCH_G(d, (actor_step_kernel<G><<<(unsigned)w.nblocks, kThreads, 0, st>>>(a)));
+  scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, counters);
+  return launch_status();
+}
+
+int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
+                  uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,
+                  const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
+                  uint64_t seed, int64_t env_base, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
+                  int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
+                  void* stream) {
+  const int rc = tc_actor_pre(qubits, syn, prev_syn, actions, reward, terminal, gs, status, steps, episode,
+                              p_thresh, counters, flags, max_steps, mode, n_fixed, seed, env_base, counts, offsets,
+                              workspace, workspace_bytes, d, n, stream);
+  if (rc != 0) return rc;
+  return tc_persp_write(syn, out, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n, stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,249 @@
+"""Device-resident batch of toric-code environments driven through the C ABI.
+
+`ToricEngine` owns the torch tensors (the library never allocates) and enqueues every call on
+torch's current CUDA stream.  The reference-shaped classes in `envs.py` and the perspective
+functions in `perspectives.py` are thin layers over it.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+SAMPLE_DEPOLARIZING = 0   # generateRandomError        (ToricCode.py:130-151)
+SAMPLE_FIXED_WEIGHT = 1   # generateNRandomErrors      (ToricCode.py:153-166)
+SAMPLE_FIXED_PLUS_P = 2   # generateNPlusQRandomErrors (results/small_p_error_test.py:43-52)
+
+ACTOR_RANDOM_ACTIONS = 1
+ACTOR_AUTO_RESET = 2
+
+STATUS_BAD_ACTION = 1
+STATUS_RESET_GAVE_UP = 2
+
+COUNTER_NAMES = ("env_steps", "episodes", "solved", "ground_kept", "timeouts", "perspectives",
+                 "err_x", "err_y", "err_z", "qubits_sampled", "reset_attempts", "bad_actions")
+
+
+def p_to_thresh(p):
+    """Error threshold used by the device sampler: a qubit errs iff its 32-bit draw < floor(p * 2^32)."""
+    p = np.asarray(p, dtype=np.float64)
+    return np.minimum(np.floor(p * 4294967296.0), 4294967295.0).astype(np.uint32)
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+class ToricEngine:
+    """n independent d x d toric codes resident on one GPU.
+
+    Device layout (include/toric_b200.h): qubits int32[n,4,d] (bit planes x0,x1,z0,z1, one row per word),
+    syn int32[n,2,d] (vertex, plaquette planes).
+    """
+
+    def __init__(self, d, n, device="cuda", seed=0, env_base=0, p_error=0.1, max_steps=75):
+        self.lib = _lib.load()
+        if not (3 <= int(d) <= 32):
+            raise ValueError("lattice size d must be in [3, 32]")
+        if not torch.cuda.is_available():
+            raise RuntimeError("ToricEngine needs a CUDA device; there is no CPU fallback")
+        self.d, self.n = int(d), int(n)
+        self.device = torch.device(device)
+        self.seed, self.env_base, self.max_steps = int(seed), int(env_base), int(max_steps)
+        dev, n_, d_ = self.device, self.n, self.d
+        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)  # noqa: E731
+        self.qubits = z((n_, 4, d_), torch.int32)
+        self.syn = z((n_, 2, d_), torch.int32)
+        self.prev_syn = None
+        self.gs = torch.ones(n_, dtype=torch.uint8, device=dev)
+        self.status = z(n_, torch.uint8)
+        self.steps = z(n_, torch.int32)
+        self.episode = z(n_, torch.int32)
+        self.p_thresh = z(n_, torch.int32)
+        self.counters = z(16, torch.int64)
+        self.actions = z((n_, 4), torch.int32)
+        self.reward = z(n_, torch.float32)
+        self.terminal = z(n_, torch.uint8)
+        self.counts = z(n_, torch.int32)
+        self.offsets = z(n_ + 1, torch.int64)
+        self.overflow = z(1, torch.int32)
+        nbytes = ctypes.c_size_t(0)
+        _lib.check(self.lib.tc_workspace_bytes(d_, n_, ctypes.byref(nbytes)), "tc_workspace_bytes")
+        self.workspace = z(max(int(nbytes.value), 256), torch.uint8)
+        self.out = None       # float32 [cap, 2, d, d]
+        self.pos = None       # uint8   [cap, 4]
+        self.cap = 0
+        self.set_p_error(p_error)
+
+    # -- configuration -------------------------------------------------------------------------
+    def set_p_error(self, p, idx=None):
+        """Scalar or per-env error probability (ToricCode.reset's p_error override, ToricCode.py:97-98)."""
+        if idx is None:
+            th = np.broadcast_to(p_to_thresh(p), (self.n,)).copy()
+            self.p_thresh.copy_(torch.from_numpy(th.view(np.int32)))
+        else:
+            idx = torch.as_tensor(idx, dtype=torch.int64, device=self.device)
+            th = np.broadcast_to(p_to_thresh(p), (idx.numel(),)).copy()
+            self.p_thresh[idx] = torch.from_numpy(th.view(np.int32)).to(self.device)
+
+    def worst_case_capacity(self):
+        return self.n * 2 * self.d * self.d
+
+    def ensure_capacity(self, cap):
+        cap = max(int(cap), 1)
+        if cap > self.cap:
+            self.out = None
+            self.pos = None
+            self.out = torch.empty((cap, 2, self.d, self.d), dtype=torch.float32, device=self.device)
+            self.pos = torch.empty((cap, 4), dtype=torch.uint8, device=self.device)
+            self.cap = cap
+
+    # -- mask injection / read-back --------------------------------------------------------------
+    def _as_u8(self, a, shape):
+        t = torch.as_tensor(np.ascontiguousarray(a) if isinstance(a, np.ndarray) else a)
+        t = t.to(device=self.device).to(torch.uint8).contiguous()
+        if tuple(t.shape) != tuple(shape):
+            raise ValueError("expected shape %s, got %s" % (tuple(shape), tuple(t.shape)))
+        return t
+
+    def set_qubits(self, codes):
+        """Inject Pauli-code masks (n,2,d,d); the syndrome is recomputed and the sticky flag cleared, as
+        the reference's scripts do by assigning env.qubit_matrix / env.state."""
+        t = self._as_u8(codes, (self.n, 2, self.d, self.d))
+        _lib.check(self.lib.tc_pack_qubits(_ptr(t), _ptr(self.qubits), self.d, self.n, _stream()), "tc_pack_qubits")
+        self.syndrome()
+        self.gs.fill_(1)
+
+    def get_qubits(self):
+        out = torch.empty((self.n, 2, self.d, self.d), dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.tc_unpack_qubits(_ptr(self.qubits), _ptr(out), self.d, self.n, _stream()),
+                   "tc_unpack_qubits")
+        return out
+
+    def set_state(self, state01):
+        t = self._as_u8(state01, (self.n, 2, self.d, self.d))
+        _lib.check(self.lib.tc_pack_state(_ptr(t), _ptr(self.syn), self.d, self.n, _stream()), "tc_pack_state")
+
+    def get_state(self, syn=None):
+        syn = self.syn if syn is None else syn
+        out = torch.empty((syn.shape[0], 2, self.d, self.d), dtype=torch.uint8, device=self.device)
+        _lib.check(self.lib.tc_unpack_state(_ptr(syn), _ptr(out), self.d, syn.shape[0], _stream()), "tc_unpack_state")
+        return out
+
+    # -- kernels ---------------------------------------------------------------------------------
+    def syndrome(self):
+        _lib.check(self.lib.tc_syndrome(_ptr(self.qubits), _ptr(self.syn), self.d, self.n, _stream()), "tc_syndrome")
+
+    def reset(self, idx=None, mode=SAMPLE_DEPOLARIZING, n_fixed=0):
+        """Resample the listed envs (all when idx is None) until each has a non-trivial syndrome."""
+        if idx is None:
+            idx_t, n_idx = None, self.n
+        else:
+            idx_t = torch.as_tensor(idx, dtype=torch.int64, device=self.device).contiguous()
+            n_idx = idx_t.numel()
+            self.steps[idx_t] = 0
+        _lib.check(self.lib.tc_reset(_ptr(self.qubits), _ptr(self.syn), _ptr(self.gs), _ptr(self.status),
+                                     _ptr(self.p_thresh), _ptr(self.episode), _ptr(idx_t), n_idx, int(mode),
+                                     int(n_fixed), self.seed, self.env_base, self.d, _stream()), "tc_reset")
+        if idx is None:
+            self.steps.zero_()
+
+    def step(self, actions):
+        """EnvSet.step: actions (n,4) int (matrix,row,col,op).  Returns (reward f32[n], terminal u8[n])."""
+        a = torch.as_tensor(actions)
+        if tuple(a.shape) != (self.n, 4):
+            raise ValueError("actions must have shape (%d, 4)" % self.n)
+        self.actions.copy_(a.to(torch.int32), non_blocking=True)
+        _lib.check(self.lib.tc_step(_ptr(self.qubits), _ptr(self.syn), _ptr(self.actions), _ptr(self.reward),
+                                    _ptr(self.terminal), _ptr(self.status), self.d, self.n, _stream()), "tc_step")
+        self.steps += 1
+        return self.reward, self.terminal
+
+    def ground_state(self):
+        _lib.check(self.lib.tc_ground_state(_ptr(self.qubits), _ptr(self.gs), self.d, self.n, _stream()),
+                   "tc_ground_state")
+        return self.gs
+
+    def perspectives(self, syn=None, n=None):
+        """Launch count + scan + write into the engine's buffers (asynchronous).  `syn` may be any packed
+        state tensor int32[n',2,d] with n' <= n."""
+        syn = self.syn if syn is None else syn
+        n = syn.shape[0] if n is None else n
+        self._last_syn = syn
+        if self.out is None:
+            self.ensure_capacity(self.worst_case_capacity())
+        self.overflow.zero_()
+        _lib.check(self.lib.tc_perspectives(_ptr(syn), _ptr(self.out), _ptr(self.pos), _ptr(self.counts),
+                                            _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace),
+                                            self.workspace.numel(), self.d, n, _stream()), "tc_perspectives")
+
+    def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False):
+        """One fused actor iteration (asynchronous).  actions=None draws them on device."""
+        flags = (ACTOR_AUTO_RESET if auto_reset else 0)
+        if actions is None:
+            flags |= ACTOR_RANDOM_ACTIONS
+        else:
+            self.actions.copy_(torch.as_tensor(actions).to(torch.int32), non_blocking=True)
+        if keep_prev and self.prev_syn is None:
+            self.prev_syn = torch.zeros_like(self.syn)
+        if self.out is None:
+            self.ensure_capacity(self.worst_case_capacity())
+        self._last_syn = self.syn
+        self.overflow.zero_()
+        _lib.check(self.lib.tc_actor_step(
+            _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(self.actions),
+            _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+            _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
+            int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(self.counts),
+            _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace), self.workspace.numel(),
+            self.d, self.n, _stream()), "tc_actor_step")
+
+    def actor_pre(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0):
+        """First half of actor_step (step / bookkeeping / count / scan) -- used with persp_write() by
+        callers that time the two halves separately (bench.py)."""
+        flags = (ACTOR_AUTO_RESET if auto_reset else 0)
+        if actions is None:
+            flags |= ACTOR_RANDOM_ACTIONS
+        else:
+            self.actions.copy_(torch.as_tensor(actions).to(torch.int32), non_blocking=True)
+        self._last_syn = self.syn
+        _lib.check(self.lib.tc_actor_pre(
+            _ptr(self.qubits), _ptr(self.syn), _ptr(None), _ptr(self.actions), _ptr(self.reward),
+            _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps), _ptr(self.episode),
+            _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode), int(n_fixed), self.seed,
+            self.env_base, _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace), self.workspace.numel(),
+            self.d, self.n, _stream()), "tc_actor_pre")
+
+    def persp_write(self):
+        """Second half: the streaming perspective write for the state left by actor_pre()."""
+        if self.out is None:
+            self.ensure_capacity(self.worst_case_capacity())
+        _lib.check(self.lib.tc_persp_write(_ptr(self.syn), _ptr(self.out), _ptr(self.pos), _ptr(self.offsets),
+                                           _ptr(self.overflow), self.cap, _ptr(self.workspace),
+                                           self.workspace.numel(), self.d, self.n, _stream()), "tc_persp_write")
+
+    # -- results ---------------------------------------------------------------------------------
+    def total_perspectives(self, n=None):
+        """Host read of offsets[n] (synchronises)."""
+        n = self.n if n is None else n
+        return int(self.offsets[n].item())
+
+    def perspective_views(self, n=None):
+        """(persp float32 (sumP,2,d,d), pos uint8 (sumP,4), counts int32 (n,), offsets int64 (n+1,)) as
+        views of the engine buffers.  Synchronises to learn sumP; regenerates if the buffer overflowed."""
+        n = self.n if n is None else n
+        total = self.total_perspectives(n)
+        if int(self.overflow.item()) != 0:
+            self.ensure_capacity(total)
+            self.perspectives(syn=getattr(self, "_last_syn", None), n=n)
+            total = self.total_perspectives(n)
+        return self.out[:total], self.pos[:total], self.counts[:n], self.offsets[:n + 1]
+
+    def read_counters(self):
+        c = self.counters.cpu().numpy()
+        return {name: int(c[i]) for i, name in enumerate(COUNTER_NAMES)}

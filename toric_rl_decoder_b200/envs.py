@@ -1,0 +1,172 @@
+"""Reference-shaped environment classes on top of the CUDA engine.
+
+`ToricCodeB200` mirrors gym_ToricCode's `ToricCode` (gym_ToricCode/gym_ToricCode/envs/ToricCode.py:8-344)
+and `EnvSetB200` mirrors `EnvSet` (src/EnvSet.py:4-51): same method names, argument meaning and return
+dtypes (int64 states, float64 rewards, bool terminals), so the reference's callers
+(src/Actor_mp.py:48-62,116,171-183; src/evaluation.py:51-113) run unchanged.  All arithmetic happens in
+libtoric_b200.so on the GPU; there is no CPU path.
+"""
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from .engine import (SAMPLE_DEPOLARIZING, SAMPLE_FIXED_WEIGHT, ToricEngine)
+
+_Box = namedtuple("Box", ["low", "high", "shape"])
+
+
+def _config(config):
+    size = config["size"] if "size" in config else 3
+    # the env reads 'min_qbit_errors' (ToricCode.py:39); the reference's callers misspell it
+    # 'min_qubit_errors' (Distributed_mp.py:73-76, evaluation.py:51) so the env silently uses 0: same here.
+    min_err = config["min_qbit_errors"] if "min_qbit_errors" in config else 0
+    p = config["p_error"] if "p_error" in config else 0.1
+    return int(size), int(min_err), float(p)
+
+
+class ToricCodeB200:
+    """Single environment = engine batch of one.  API of ToricCode (ToricCode.py:24-88, :90-218, :289-337).
+
+    `qubit_matrix` and `state` are read/write properties that unpack / pack the device bit planes; the
+    setters are the mask-injection interface the reference's scripts use
+    (results/small_p_error_test.py:119-120, results/start_from_state.py:36-38)."""
+
+    metadata = {"render.modes": ["human"]}
+
+    def __init__(self, config=None, device="cuda", seed=0, env_base=0):
+        config = config or {}
+        self.system_size, self.min_qbit_errors, self.p_error = _config(config)
+        d = self.system_size
+        self.action_space = _Box(np.array([0, 0, 0, 0]), np.array([1, d, d, 3]), (4,))
+        self.observation_space = _Box(0, 1, (2, d, d))
+        self.rule_table = np.array([[0, 1, 2, 3], [1, 0, 3, 2], [2, 3, 0, 1], [3, 2, 1, 0]], dtype=int)
+        self._eng = ToricEngine(d, 1, device=device, seed=seed, env_base=env_base, p_error=self.p_error)
+        self.next_state = self.state
+
+    # -- attribute surface -------------------------------------------------------------------------
+    @property
+    def qubit_matrix(self):
+        return self._eng.get_qubits()[0].cpu().numpy().astype(np.int64)
+
+    @qubit_matrix.setter
+    def qubit_matrix(self, q):
+        # the reference assigns qubit_matrix and state separately; here the syndrome follows the qubits
+        self._eng.set_qubits(np.asarray(q).astype(np.uint8)[None])
+
+    @property
+    def state(self):
+        return self._eng.get_state()[0].cpu().numpy().astype(np.int64)
+
+    @state.setter
+    def state(self, s):
+        self._eng.set_state((np.asarray(s) != 0).astype(np.uint8)[None])
+
+    @property
+    def ground_state(self):
+        return bool(self._eng.gs[0].item())
+
+    @ground_state.setter
+    def ground_state(self, v):
+        self._eng.gs.fill_(1 if v else 0)
+
+    # -- gym API -----------------------------------------------------------------------------------
+    def reset(self, p_error=None):
+        """ToricCode.reset (ToricCode.py:90-127)."""
+        if p_error is not None:
+            self.p_error = p_error
+        self._eng.set_p_error(self.p_error)
+        if self.min_qbit_errors == 0:
+            self._eng.reset(mode=SAMPLE_DEPOLARIZING)
+        else:
+            self._eng.reset(mode=SAMPLE_FIXED_WEIGHT, n_fixed=self.min_qbit_errors)
+        return self.state
+
+    def step(self, action):
+        """ToricCode.step (ToricCode.py:62-88): returns (state, reward, terminal, {})."""
+        a = np.asarray(action, dtype=np.int64).reshape(1, 4)
+        reward, terminal = self._eng.step(torch.from_numpy(a))
+        r = reward[0].item()
+        self.next_state = self.state
+        return self.next_state, int(r), bool(terminal[0].item()), {}
+
+    def createSyndromOpt(self, tcode):
+        """createSyndromOpt (ToricCode.py:168-199) of an arbitrary qubit matrix (scratch engine state)."""
+        eng = ToricEngine(self.system_size, 1, device=self._eng.device)
+        eng.set_qubits(np.asarray(tcode).astype(np.uint8)[None])
+        return eng.get_state()[0].cpu().numpy().astype(np.int64)
+
+    def isTerminalState(self, state):
+        return bool(np.all(np.asarray(state) == 0))
+
+    def evalGroundState(self):
+        """evalGroundState (ToricCode.py:289-337), sticky until reset."""
+        return bool(self._eng.ground_state()[0].item())
+
+    def generateRandomError(self, matrix, p_error):
+        """generateRandomError (ToricCode.py:130-151) drawn by the device sampler (no rejection)."""
+        raise NotImplementedError("use reset(); the device sampler always applies the non-trivial-syndrome rejection")
+
+    def render(self, mode="human"):
+        pass
+
+    def close(self):
+        pass
+
+
+class EnvSetB200:
+    """EnvSet (src/EnvSet.py:4-51) over one engine batch.
+
+    With numpy_compat=True (default) results come back as the reference's numpy dtypes; with False they
+    stay on the device as torch tensors (uint8 states, float32 rewards, bool terminals) and nothing
+    synchronises."""
+
+    def __init__(self, env, no_envs, device="cuda", seed=0, env_base=0, numpy_compat=True):
+        if isinstance(env, dict):
+            size, min_err, p = _config(env)
+        else:
+            size, min_err, p = env.system_size, getattr(env, "min_qbit_errors", 0), env.p_error
+        self.size = size
+        self.no_envs = int(no_envs)
+        self.min_qbit_errors = int(min_err)
+        self.numpy_compat = numpy_compat
+        self.engine = ToricEngine(size, self.no_envs, device=device, seed=seed, env_base=env_base, p_error=p)
+        self.states = self._states()
+
+    def _states(self):
+        st = self.engine.get_state()
+        return st.cpu().numpy().astype(np.int64) if self.numpy_compat else st
+
+    def _reset(self, idx):
+        if self.min_qbit_errors == 0:
+            self.engine.reset(idx, mode=SAMPLE_DEPOLARIZING)
+        else:
+            self.engine.reset(idx, mode=SAMPLE_FIXED_WEIGHT, n_fixed=self.min_qbit_errors)
+
+    def resetAll(self, p_errors=None):
+        """EnvSet.resetAll (src/EnvSet.py:28-36)."""
+        if p_errors is not None:
+            self.engine.set_p_error(np.asarray(p_errors, dtype=np.float64))
+        self._reset(None)
+        self.states = self._states()
+        return self.states
+
+    def resetTerminalEnvs(self, idx, p_errors=None):
+        """EnvSet.resetTerminalEnvs (src/EnvSet.py:19-26): returns float64 states of the listed envs."""
+        idx = np.asarray(idx, dtype=np.int64).reshape(-1)
+        if p_errors is not None:
+            self.engine.set_p_error(np.asarray(p_errors, dtype=np.float64), idx=idx)
+        self._reset(idx)
+        it = torch.as_tensor(idx, device=self.engine.device)
+        st = self.engine.get_state(self.engine.syn[it].contiguous())
+        return st.cpu().numpy().astype(np.float64) if self.numpy_compat else st
+
+    def step(self, actions):
+        """EnvSet.step (src/EnvSet.py:38-47): (states, rewards, terminals, info)."""
+        a = torch.as_tensor(np.asarray(actions, dtype=np.int64) if not torch.is_tensor(actions) else actions)
+        reward, terminal = self.engine.step(a)
+        st = self.engine.get_state()
+        if self.numpy_compat:
+            return (st.cpu().numpy().astype(np.int64), reward.cpu().numpy().astype(np.float64),
+                    terminal.cpu().numpy().astype(bool), {})
+        return st, reward, terminal.bool(), {}

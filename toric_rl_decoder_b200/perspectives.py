@@ -1,0 +1,60 @@
+"""generatePerspective / generatePerspectiveOptimized / generatePerspectiveBatch on the GPU.
+
+Same names and argument order as src/util.py:46-150 and src/numba/util_actor.py:56-67.  The batch form
+returns the select-action input layout of src/numba/util_actor.py:35-39 directly: one float32 tensor
+(sumP,2,d,d) on the device, positions (sumP,3), counts (N,) and offsets (N+1,) with
+offsets[1:] == np.cumsum(counts) == the reference's splice_idx.
+"""
+from collections import namedtuple
+
+import numpy as np
+import torch
+
+from .engine import ToricEngine
+
+Perspective = namedtuple("Perspective", ["perspective", "position"])   # src/util.py:12
+
+_engines = {}
+
+
+def _engine(d, n, device):
+    key = (d, str(device))
+    eng = _engines.get(key)
+    if eng is None or eng.n < n:
+        eng = ToricEngine(d, max(n, 1), device=device)
+        _engines[key] = eng
+    return eng
+
+
+def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda"):
+    """states: (N,2,d,d) array/tensor of 0/1.  Returns (perspectives f32 (sumP,2,d,d) cuda tensor,
+    positions int64 (sumP,3) cuda tensor, counts int32 (N,), offsets int64 (N+1,))."""
+    d = int(toric_size)
+    if int(grid_shift) != d // 2:
+        raise ValueError("grid_shift must be toric_size // 2 (src/Actor_mp.py:59)")
+    st = torch.as_tensor(np.ascontiguousarray(states) if isinstance(states, np.ndarray) else states)
+    n = st.shape[0]
+    eng = _engine(d, n, device)
+    syn = torch.zeros((n, 2, d), dtype=torch.int32, device=eng.device)
+    u8 = (st != 0).to(device=eng.device, dtype=torch.uint8).contiguous()
+    from . import _lib
+    from .engine import _ptr, _stream
+    _lib.check(eng.lib.tc_pack_state(_ptr(u8), _ptr(syn), d, n, _stream()), "tc_pack_state")
+    eng.perspectives(syn=syn, n=n)
+    persp, pos, counts, offsets = eng.perspective_views(n)
+    return persp, pos[:, :3].to(torch.int64), counts, offsets
+
+
+def generatePerspectiveOptimized(grid_shift, toric_size, state, device="cuda"):
+    """src/util.py:106-150: returns (list of (2,d,d) arrays, list of (m,i,j) tuples), same dtype as input."""
+    state = np.asarray(state)
+    persp, pos, _, _ = generatePerspectiveBatch(grid_shift, toric_size, state[None], device=device)
+    views = persp.cpu().numpy().astype(state.dtype)
+    pos = pos.cpu().numpy()
+    return [v for v in views], [tuple(int(x) for x in p) for p in pos]
+
+
+def generatePerspective(grid_shift, toric_size, state, device="cuda"):
+    """src/util.py:46-85: returns [Perspective(array, (m,i,j)), ...]."""
+    views, pos = generatePerspectiveOptimized(grid_shift, toric_size, state, device=device)
+    return [Perspective(v, p) for v, p in zip(views, pos)]
