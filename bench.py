@@ -61,54 +61,68 @@ def write_kernel_bytes(d, n_envs, sum_p):
 
 # ----------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled through NVML from a background thread DURING the timed
+    region (the timed region is tens of milliseconds, too short for `nvidia-smi -lms`)."""
 
-    def __init__(self, gpu_index=0):
-        self.gpu_index, self.proc, self.path = gpu_index, None, None
+    def __init__(self, gpu_index=0, period_s=0.002):
+        self.gpu_index, self.period = gpu_index, period_s
+        self.sm, self.reasons, self.sm_max = [], set(), None
+        self._stop = False
+        self._thread = None
+        self._h = None
+
+    def _loop(self):
+        import pynvml as nv
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown")
+                else nv.nvmlClocksThrottleReasonHwSlowdown,
+                "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown",
+                                               getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40)),
+                "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown",
+                                               getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20)),
+                "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap",
+                                        getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4))}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons",
+                              getattr(nv, "nvmlDeviceGetCurrentClocksThrottleReasons", None))
+        while not self._stop:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                if get_reasons is not None:
+                    r = int(get_reasons(self._h))
+                    for name, bit in bits.items():
+                        if r & int(bit):
+                            self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(self.period)
 
     def __enter__(self):
         try:
-            fd, self.path = tempfile.mkstemp(suffix=".csv")
-            os.close(fd)
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu_index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+            import threading
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = self.gpu_index
+            if vis:
+                try:
+                    idx = int(vis.split(",")[self.gpu_index])
+                except Exception:
+                    pass
+            self._h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(nv.nvmlDeviceGetMaxClockInfo(self._h, nv.NVML_CLOCK_SM))
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
         except Exception:
-            self.proc = None
+            self._thread = None
         return self
 
     def __exit__(self, *exc):
-        if self.proc is not None:
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=5)
-            except Exception:
-                self.proc.kill()
+        self._stop = True
+        if self._thread is not None:
+            self._thread.join(timeout=2)
 
     def summary(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        if not self.path or not os.path.exists(self.path):
-            return out
-        sm, mx, reasons = [], [], set()
-        for line in open(self.path):
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 9:
-                continue
-            try:
-                sm.append(float(f[1]))
-                mx.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        os.unlink(self.path)
-        if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
-        return out
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "how": "NVML, 2 ms period, timed region only"}
 
 
 def load_peaks():
@@ -179,15 +193,13 @@ def run_b200(a):
     import torch
     import toric_rl_decoder_b200 as pkg
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
+    from toric_rl_decoder_b200 import sharding
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    rank, world, local = sharding.init_from_env("nccl")     # one process per GPU (torchrun env)
     dist = None
     if world > 1:
         import torch.distributed as dist
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     d, n = a.d, a.envs
 
@@ -222,11 +234,8 @@ def run_b200(a):
     write_ms = sum(b.elapsed_time(c) for b, c in zip(evb, evc)) / a.steps
     ctr = eng.counters.clone()
     assert int(eng.overflow.item()) == 0
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)           # time = max over ranks
-        dist.all_reduce(ctr, op=dist.ReduceOp.SUM)         # the path's only collective: counter all-reduce
-    ms = float(t.item())
+    ms = sharding.max_over_ranks(ms, dev)                  # time = max over ranks
+    sharding.allreduce_counters(ctr)                       # the path's only collective: counter all-reduce
     c = {name: int(ctr[i].item()) for i, name in enumerate(pkg.engine.COUNTER_NAMES)}
     total_steps = c["env_steps"]
     assert total_steps == n * a.steps * world
@@ -318,10 +327,8 @@ def run_e2e(a, eng, dev, dist, barrier, world):
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    from toric_rl_decoder_b200 import sharding
+    ms = sharding.max_over_ranks(ms, dev)
     dc = eng.counters - c0
     return {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
             "d2h_bytes_per_step": d2h, "ms_per_step": ms / a.steps,
