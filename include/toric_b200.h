@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 1
+#define TC_ABI_VERSION 2
 #define TC_NUM_COUNTERS 16
 
 /* status bits written per env */
@@ -43,6 +43,11 @@ extern "C" {
 /* flags of tc_actor_step */
 #define TC_ACTOR_RANDOM_ACTIONS 1 /* draw the action on device (uniform over the perspective list x {X,Y,Z}) */
 #define TC_ACTOR_AUTO_RESET 2     /* reset envs that are terminal or past max_steps (Actor_mp.py:171-183) */
+#define TC_ACTOR_FREEZE_DONE 4    /* leave already-solved envs untouched (batched evaluation.py:79 loop exit) */
+
+/* element types of tc_transitions outputs */
+#define TC_DTYPE_F32 0
+#define TC_DTYPE_U8 1
 
 int tc_abi_version(void);
 
@@ -120,6 +125,46 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
                  const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
                  uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
                  size_t workspace_bytes, int d, int64_t n, void* stream);
+
+/* ---- policy-side entry points (the callers either side of the env path) ---- */
+
+/* _selectActionBatch_prime + the epsilon-greedy draw of selectActionBatch (src/numba/util_actor.py:41-107;
+ * single-env form src/util_actor.py:47-65).  One segment of Q-value rows per env:
+ *   q_values  float32 [sumP][3]   network output for the perspectives of tc_perspectives / tc_actor_step
+ *   pos       uint8   [sumP][4]   their (m,i,j,0) positions;  offsets int64 [n+1]
+ *   actions   int32   [n][4]      out: (m, i, j, a+1) of the chosen (perspective, action)
+ *   q_sel     float32 [n][3]      out: the Q-value row of the chosen perspective (reference's q_v)
+ *   sel_idx   int64   [n]         out: global row of the chosen perspective, -1 when the env has none (nullable)
+ *   was_greedy uint8  [n]         out: 1 greedy / 0 random (nullable)
+ * Greedy = first maximum in row-major (perspective, action) order (np.argmax tie-break).  The decision is
+ * drawn on device: Philox(seed; env_base+e, episode[e], 0x40000000|steps[e]) -> random iff u0 < eps
+ * threshold (eps_thresh uint32 [n] per env, or eps_scalar when NULL; threshold = floor(eps * 2^32)),
+ * random perspective mulhi(u1, P), random action mulhi(u2, 3); greedy_in (uint8 [n], nullable) overrides
+ * the decision.  episode / steps nullable (0).  Envs without perspectives get the identity action
+ * (0,0,0,0) and q_sel = 0. */
+int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* offsets, const uint32_t* episode,
+                     const int32_t* steps, const uint32_t* eps_thresh, uint32_t eps_scalar,
+                     const uint8_t* greedy_in, uint64_t seed, int64_t env_base, int32_t* actions, float* q_sel,
+                     int64_t* sel_idx, uint8_t* was_greedy, int64_t n, void* stream);
+
+/* generateTransitionParallel's state pair (src/util_actor.py:223-264): both syndromes rolled so the acted
+ * qubit sits at (g,g) (shift_state, src/util.py:97-102) and rotated when it lives in matrix 1
+ * (rotate_state, src/util.py:87-94).  out_prev / out_next: [n][2][d][d] of out_dtype (TC_DTYPE_F32 or
+ * TC_DTYPE_U8), either nullable;  action_out int32 [n][4] = (m, g, g, op), nullable. */
+int tc_transitions(const uint32_t* syn_prev, const uint32_t* syn_next, const int32_t* actions, void* out_prev,
+                   void* out_next, int32_t* action_out, int out_dtype, int d, int64_t n, void* stream);
+
+/* computePrioritiesParallel (src/util_actor.py:268-287): |reward + discount * max_a q_next[a] - q[op-1]|.
+ * actions int32 [n][4]; q, q_next float32 [n][3]; priorities float32 [n]. */
+int tc_td_priorities(const int32_t* actions, const float* reward, const float* q, const float* q_next,
+                     float discount, float* priorities, int64_t n, void* stream);
+
+/* The per-state maximum of predictMaxOptimized (src/util_learner.py:88-111): max over the state's Q-value
+ * segment; states with fewer perspectives than pad_to (the batch maximum; read from *pad_to_dev when that
+ * is non-NULL) also compete against 0 (the reference zero-pads, :100-106); states without perspectives
+ * give 0 (:109). */
+int tc_segmented_max(const float* q_values, const int64_t* offsets, int pad_to, const int32_t* pad_to_dev,
+                     float* out, int64_t n, void* stream);
 
 #ifdef __cplusplus
 }

@@ -208,3 +208,58 @@ def transition_views(action, state, next_state):
     if m == 1:
         ps, ns = rotate_state(ps), rotate_state(ns)
     return ps, (m, g, g, op), ns
+
+
+# --------------------------------------------------------------------------------------------------
+# policy-side restatements
+# --------------------------------------------------------------------------------------------------
+def select_action_prime(q_values_table, offsets, positions, greedy, rand_p=None, rand_a=None):
+    """_selectActionBatch_prime (src/numba/util_actor.py:69-107): per env the first maximum of its
+    Q-value rows in row-major (perspective, action) order, or the supplied random pick; returns
+    (actions int64 (n,4), q_v float (n,3), chosen global row (n,)).  Envs without rows get the identity
+    action (0,0,0,0) (the reference would fail on an empty slice; the device path defines this)."""
+    q = np.asarray(q_values_table)
+    n = len(offsets) - 1
+    actions = np.zeros((n, 4), np.int64)
+    q_v = np.zeros((n, 3), q.dtype)
+    rows = np.full(n, -1, np.int64)
+    for e in range(n):
+        a0, a1 = int(offsets[e]), int(offsets[e + 1])
+        if a1 == a0:
+            continue
+        seg = q[a0:a1]
+        if greedy[e]:
+            p, a = np.unravel_index(np.argmax(seg, axis=None), seg.shape)   # src/util_actor.py:51
+        else:
+            p, a = int(rand_p[e]), int(rand_a[e])
+        q_v[e] = seg[p]
+        actions[e] = (positions[a0 + p][0], positions[a0 + p][1], positions[a0 + p][2], a + 1)
+        rows[e] = a0 + p
+    return actions, q_v, rows
+
+
+def td_priorities(actions, reward, q, q_next, discount):
+    """computePrioritiesParallel (src/util_actor.py:268-287) on flat (n,...) arrays, float32 arithmetic."""
+    q = np.asarray(q, np.float32)
+    qn = np.asarray(q_next, np.float32).max(axis=-1)
+    a = np.asarray(actions)[..., 3] - 1
+    qv = np.take_along_axis(q, a[..., None], axis=-1)[..., 0]
+    return np.abs(np.asarray(reward, np.float32) + np.float32(discount) * qn - qv)
+
+
+def predict_max(q_values_table, offsets):
+    """The reduction of predictMaxOptimized (src/util_learner.py:83-111): terminal states count as one
+    (zero) perspective for the padding width and yield 0; shorter segments are zero-padded before argmax."""
+    q = np.asarray(q_values_table, np.float32)
+    n = len(offsets) - 1
+    counts = np.diff(np.asarray(offsets))
+    largest = int(max(1, counts.max())) if n else 0
+    out = np.zeros(n, np.float32)
+    for e in range(n):
+        if counts[e] == 0:
+            continue
+        seg = q[int(offsets[e]):int(offsets[e + 1])].reshape(-1)
+        if counts[e] < largest:
+            seg = np.concatenate((seg, np.zeros(1, np.float32)))
+        out[e] = seg.max()
+    return out

@@ -10,3 +10,5 @@ from .engine import (ACTOR_AUTO_RESET, ACTOR_RANDOM_ACTIONS, SAMPLE_DEPOLARIZING
 from .envs import EnvSetB200, ToricCodeB200  # noqa: F401
 from .perspectives import (Perspective, generatePerspective, generatePerspectiveBatch,  # noqa: F401
                            generatePerspectiveOptimized)
+from .policy import (computePrioritiesParallel, generateTransitionParallel, predictMaxOptimized,  # noqa: F401
+                     selectAction, selectActionBatch, select_action_device, transitions_device)

@@ -30,8 +30,13 @@ SIGNATURES = {
                      _vp, _vp, _vp, _sz, _i, _i64, _vp],
     "tc_actor_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
                       _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_select_action": [_vp, _vp, _vp, _vp, _vp, _vp, _c.c_uint32, _vp, _u64, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
+    "tc_transitions": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i64, _vp],
+    "tc_td_priorities": [_vp, _vp, _vp, _vp, _c.c_float, _vp, _i64, _vp],
+    "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],
 }
 
+ABI_VERSION = 2
 _lib = None
 
 
@@ -49,7 +54,7 @@ def load():
         fn = getattr(lib, name)      # AttributeError if the symbol is missing
         fn.argtypes = argtypes
         fn.restype = _i
-    if lib.tc_abi_version() != 1:
+    if lib.tc_abi_version() != ABI_VERSION:
         raise RuntimeError("libtoric_b200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -10,7 +10,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libtoric_b200.so")
 SOURCES = [os.path.join(CSRC, "toric_b200.cu")]
-HEADERS = [os.path.join(CSRC, h) for h in ("common.cuh", "state_kernels.cuh", "persp_write.cuh")] + \
+HEADERS = [os.path.join(CSRC, h) for h in ("common.cuh", "state_kernels.cuh", "persp_write.cuh", "policy_kernels.cuh")] + \
           [os.path.join(os.path.dirname(PKG_DIR), "include", "toric_b200.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -4,6 +4,7 @@
 
 #include "common.cuh"
 #include "persp_write.cuh"
+#include "policy_kernels.cuh"
 #include "state_kernels.cuh"
 
 namespace tc {
@@ -297,12 +298,15 @@ __global__ void __launch_bounds__(kThreads) actor_step_kernel(const ActorArgs a)
     am = act.x; ai = act.y; aj = act.z; aop = act.w;
   }
   const int before = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
-  const bool ok = apply_action<G>(d, r, am, ai, aj, aop, s);
+  // TC_ACTOR_FREEZE_DONE: an env that is already solved is left exactly as it is (batched evaluation keeps
+  // finished episodes in the batch; the reference's per-episode while loop simply ends, evaluation.py:79)
+  const bool frozen = (a.flags & TC_ACTOR_FREEZE_DONE) && before == 0;
+  const bool ok = frozen ? true : apply_action<G>(d, r, am, ai, aj, aop, s);
   const int after = gsum<G>(gmask, __popc(s.v) + __popc(s.pl));
   const bool term = after == 0;
   const bool even = parity_even<G>(gmask, s);
-  stp += 1;
-  if (lead) {
+  if (!frozen) stp += 1;
+  if (lead && !frozen) {
     a.reward[e] = term ? 100.0f : (float)(before - after);
     a.terminal[e] = term ? 1 : 0;
     a.gs[e] = even ? 1 : 0;
@@ -314,7 +318,7 @@ __global__ void __launch_bounds__(kThreads) actor_step_kernel(const ActorArgs a)
   }
   if (a.prev_syn && valid) store_syn<G>(a.prev_syn, e, d, r, s);
 
-  const bool done = term || stp > a.max_steps;      // Actor_mp.py:171-172
+  const bool done = !frozen && (term || stp > a.max_steps);      // Actor_mp.py:171-172
   if ((a.flags & TC_ACTOR_AUTO_RESET) && done) {     // uniform inside the group
     uint8_t st = 0;
     SampleStats stats;
@@ -574,6 +578,57 @@ int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* 
                               workspace, workspace_bytes, d, n, stream);
   if (rc != 0) return rc;
   return tc_persp_write(syn, out, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n, stream);
+}
+
+// ---- policy-side entry points ---------------------------------------------
+
+int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* offsets, const uint32_t* episode,
+                     const int32_t* steps, const uint32_t* eps_thresh, uint32_t eps_scalar,
+                     const uint8_t* greedy_in, uint64_t seed, int64_t env_base, int32_t* actions, float* q_sel,
+                     int64_t* sel_idx, uint8_t* was_greedy, int64_t n, void* stream) {
+  if (n < 0 || !q_values || !pos || !offsets || !actions || !q_sel) return -1;
+  if (((uintptr_t)actions & 15) || ((uintptr_t)pos & 3)) return -1;
+  if (n == 0) return 0;
+  select_action_kernel<<<grid_for(n * 32, 256), 256, 0, (cudaStream_t)stream>>>(
+      q_values, pos, offsets, episode, steps, eps_thresh, eps_scalar, greedy_in, make_key(seed), env_base, actions,
+      q_sel, sel_idx, was_greedy, n);
+  return launch_status();
+}
+
+int tc_transitions(const uint32_t* syn_prev, const uint32_t* syn_next, const int32_t* actions, void* out_prev,
+                   void* out_next, int32_t* action_out, int out_dtype, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !actions) return -1;
+  if ((out_prev && !syn_prev) || (out_next && !syn_next)) return -1;
+  if (((uintptr_t)actions & 15) || ((uintptr_t)action_out & 15)) return -1;
+  if (out_dtype != TC_DTYPE_F32 && out_dtype != TC_DTYPE_U8) return -1;
+  if (n == 0) return 0;
+  const unsigned grid = grid_for(n * 2 * d * d, 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (out_dtype == TC_DTYPE_F32)
+    transition_kernel<float><<<grid, 256, 0, st>>>(syn_prev, syn_next, actions, (float*)out_prev, (float*)out_next,
+                                                   action_out, d, n);
+  else
+    transition_kernel<uint8_t><<<grid, 256, 0, st>>>(syn_prev, syn_next, actions, (uint8_t*)out_prev,
+                                                     (uint8_t*)out_next, action_out, d, n);
+  return launch_status();
+}
+
+int tc_td_priorities(const int32_t* actions, const float* reward, const float* q, const float* q_next,
+                     float discount, float* priorities, int64_t n, void* stream) {
+  if (n < 0 || !actions || !reward || !q || !q_next || !priorities) return -1;
+  if (n == 0) return 0;
+  td_priority_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(actions, reward, q, q_next, discount,
+                                                                        priorities, n);
+  return launch_status();
+}
+
+int tc_segmented_max(const float* q_values, const int64_t* offsets, int pad_to, const int32_t* pad_to_dev,
+                     float* out, int64_t n, void* stream) {
+  if (n < 0 || !q_values || !offsets || !out) return -1;
+  if (n == 0) return 0;
+  segmented_max_kernel<<<grid_for(n * 32, 256), 256, 0, (cudaStream_t)stream>>>(q_values, offsets, pad_to,
+                                                                               pad_to_dev, out, n);
+  return launch_status();
 }
 
 }  // extern "C"

@@ -17,6 +17,7 @@ SAMPLE_FIXED_PLUS_P = 2   # generateNPlusQRandomErrors (results/small_p_error_te
 
 ACTOR_RANDOM_ACTIONS = 1
 ACTOR_AUTO_RESET = 2
+ACTOR_FREEZE_DONE = 4
 
 STATUS_BAD_ACTION = 1
 STATUS_RESET_GAVE_UP = 2
@@ -182,12 +183,15 @@ class ToricEngine:
                                             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace),
                                             self.workspace.numel(), self.d, n, _stream()), "tc_perspectives")
 
-    def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False):
-        """One fused actor iteration (asynchronous).  actions=None draws them on device."""
-        flags = (ACTOR_AUTO_RESET if auto_reset else 0)
+    def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
+                   freeze_done=False):
+        """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
+        self.actions itself (e.g. filled by select_action) skips the copy.  freeze_done leaves envs whose
+        syndrome is already trivial untouched (batched evaluation)."""
+        flags = (ACTOR_AUTO_RESET if auto_reset else 0) | (ACTOR_FREEZE_DONE if freeze_done else 0)
         if actions is None:
             flags |= ACTOR_RANDOM_ACTIONS
-        else:
+        elif actions is not self.actions:
             self.actions.copy_(torch.as_tensor(actions).to(torch.int32), non_blocking=True)
         if keep_prev and self.prev_syn is None:
             self.prev_syn = torch.zeros_like(self.syn)

@@ -26,9 +26,10 @@ def _engine(d, n, device):
     return eng
 
 
-def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda"):
+def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda", raw_positions=False):
     """states: (N,2,d,d) array/tensor of 0/1.  Returns (perspectives f32 (sumP,2,d,d) cuda tensor,
-    positions int64 (sumP,3) cuda tensor, counts int32 (N,), offsets int64 (N+1,))."""
+    positions int64 (sumP,3) cuda tensor, counts int32 (N,), offsets int64 (N+1,)).  raw_positions=True keeps
+    the positions as the device layout uint8 (sumP,4) = (m,i,j,0) that tc_select_action consumes."""
     d = int(toric_size)
     if int(grid_shift) != d // 2:
         raise ValueError("grid_shift must be toric_size // 2 (src/Actor_mp.py:59)")
@@ -42,6 +43,8 @@ def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda"):
     _lib.check(eng.lib.tc_pack_state(_ptr(u8), _ptr(syn), d, n, _stream()), "tc_pack_state")
     eng.perspectives(syn=syn, n=n)
     persp, pos, counts, offsets = eng.perspective_views(n)
+    if raw_positions:
+        return persp, pos, counts, offsets
     return persp, pos[:, :3].to(torch.int64), counts, offsets
 
 
