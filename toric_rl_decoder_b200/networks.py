@@ -5,7 +5,7 @@ Table-driven restatement of the reference's plain CNN decoders (src/nn/torch/NN.
 convolutions with the channel schedule below, a last valid 3x3 convolution and one linear layer to the 3
 Pauli Q-values.  Parameter names (conv1..convN, linear1) match the reference so its state_dicts load
 unchanged (network/converged/*.pt; the legacy full-module pickle network/Size_5_NN_11.pt has to be
-converted to a state_dict by the reference's own loader first, see oracle/gen_golden_rollout.py).
+converted to a state_dict by the reference's own loader first; tests/golden/ holds the converted files).
 """
 import torch
 import torch.nn as nn
