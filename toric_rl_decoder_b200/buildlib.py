@@ -8,7 +8,8 @@ import subprocess
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
-LIB_PATH = os.path.join(PKG_DIR, "libtoric_b200.so")
+# TORIC_B200_LIB selects another build of the same sources (kernel-variant experiments); default: in-tree
+LIB_PATH = os.environ.get("TORIC_B200_LIB") or os.path.join(PKG_DIR, "libtoric_b200.so")
 SOURCES = [os.path.join(CSRC, "toric_b200.cu")]
 HEADERS = [os.path.join(CSRC, h) for h in ("common.cuh", "state_kernels.cuh", "persp_write.cuh", "policy_kernels.cuh")] + \
           [os.path.join(os.path.dirname(PKG_DIR), "include", "toric_b200.h")]
@@ -24,8 +25,15 @@ def is_stale():
     return any(os.path.getmtime(p) > t for p in SOURCES + HEADERS)
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), out=None):
     """Compile the CUDA library for sm_100a.  Returns the path of the .so."""
+    if out is not None:
+        nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+        cmd = [nvcc] + NVCC_FLAGS + ["-D%s" % d for d in defines] + ["-o", out] + SOURCES
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError("nvcc failed:\n%s\n%s" % (" ".join(cmd), res.stderr))
+        return out
     if not force and not is_stale():
         return LIB_PATH
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -407,9 +407,15 @@ inline Workspace carve(void* ws, int d, int64_t n) {
 template <int D>
 void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
                   int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
-  constexpr int WPB = PerspCfg<D>::kWarps;
-  persp_write_kernel<D><<<grid_for(n, WPB), WPB * 32, 0, st>>>(syn, w.local_off, w.block_off, w.epb, out, pos,
-                                                               offsets, overflow, cap, n);
+  using Cfg = PerspCfg<D>;
+  constexpr int WPB = Cfg::kWarps;
+  static bool configured = false;                 // opt in to > 48 KB of dynamic shared memory once per size
+  if (!configured) {
+    cudaFuncSetAttribute(persp_write_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    configured = true;
+  }
+  persp_write_kernel<D><<<grid_for(n, WPB), WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb,
+                                                                           out, pos, offsets, overflow, cap, n);
 }
 
 int write_dispatch(int d, const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
