@@ -11,11 +11,11 @@ timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; ech
 cat gpurun_out/bench.json
 timeout 300 python bench.py --impl reference --steps 20 --warmup 3 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
 cat gpurun_out/bench_ref.json
-NCU_CMD="python bench.py --steps 5 --warmup 3 --no-cpu-baseline --no-e2e"
+NCU_CMD="python bench.py --steps 5 --warmup 80 --no-cpu-baseline --no-e2e"   # steady state: P/env has saturated after ~75 steps
 timeout 300 $NCU_CMD > gpurun_out/plain.log 2>&1 &&
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches.csv $NCU_CMD > gpurun_out/ncu_launch.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/launches.csv $NCU_CMD > gpurun_out/ncu_launch.log 2>&1
 timeout 300 $NCU_CMD > gpurun_out/plain2.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:persp_write -s 4 -c 2 -o gpurun_out/prof_write -f $NCU_CMD > gpurun_out/ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:persp_write -s 81 -c 2 -o gpurun_out/prof_write -f $NCU_CMD > gpurun_out/ncu_full.log 2>&1
 timeout 300 $NCU_CMD > gpurun_out/plain3.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:actor_step -s 4 -c 2 -o gpurun_out/prof_actor -f $NCU_CMD > gpurun_out/ncu_full2.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:actor_step -s 81 -c 2 -o gpurun_out/prof_actor -f $NCU_CMD > gpurun_out/ncu_full2.log 2>&1
 ls -la gpurun_out

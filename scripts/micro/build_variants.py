@@ -4,13 +4,15 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 from toric_rl_decoder_b200 import buildlib
 VAR = {
-    "w4_s1": ["TC_WRITE_WARPS=4", "TC_STAGE_BUFS=1"],
-    "w4_s2": ["TC_WRITE_WARPS=4", "TC_STAGE_BUFS=2"],
-    "w2_s1": ["TC_WRITE_WARPS=2", "TC_STAGE_BUFS=1"],
-    "w2_s2": ["TC_WRITE_WARPS=2", "TC_STAGE_BUFS=2"],
-    "w8_s1": ["TC_WRITE_WARPS=8", "TC_STAGE_BUFS=1"],
-    "w6_s1": ["TC_WRITE_WARPS=6", "TC_STAGE_BUFS=1"],
-    "w4_s1_t2": ["TC_WRITE_WARPS=4", "TC_STAGE_BUFS=1", "TC_TILE_WPL=2"],
+    "g0_w4_s1_t2": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=1", "TC_TILE_WPL=2"],
+    "g0_w4_s2_t1": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=2", "TC_TILE_WPL=1"],
+    "g0_w2_s2_t1": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=2", "TC_STAGE_BUFS=2", "TC_TILE_WPL=1"],
+    "g0_w2_s1_t2": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=2", "TC_STAGE_BUFS=1", "TC_TILE_WPL=2"],
+    "g0_w4_s3_t1": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=3", "TC_TILE_WPL=1"],
+    "g0_w1_s2_t2": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=1", "TC_STAGE_BUFS=2", "TC_TILE_WPL=2"],
+    "g4_w4_s1_t2": ["TC_WRITE_WAVES=4", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=1", "TC_TILE_WPL=2"],
+    "g4_w4_s3_t1": ["TC_WRITE_WAVES=4", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=3", "TC_TILE_WPL=1"],
+    "g0_w4_s2_t2": ["TC_WRITE_WAVES=0", "TC_WRITE_WARPS=4", "TC_STAGE_BUFS=2", "TC_TILE_WPL=2"],
 }
 out_dir = os.path.join(ROOT, "scripts", "micro", "variants")
 os.makedirs(out_dir, exist_ok=True)

@@ -2,17 +2,23 @@
 // generatePerspectiveBatch + np.concatenate + float32 cast (src/numba/util_actor.py:33-39, :56-67)
 // as one streaming kernel whose global writes are TMA bulk stores.
 //
-// One warp per environment.  The env's output is one contiguous run of P * 2d^2 floats starting at
-// float index offsets[e] * 2d^2 (always even, so 8-byte aligned; 16-byte aligned after peeling a
-// 2-float "phantom" head that belongs to the previous env).  The run is produced as a BIT stream first
-// (bit t = output float t), 32 words = 1024 floats = one 4 KB tile at a time:
-//   1. lane L assembles word L of the tile (two code paths, below);
-//   2. the 32 words are expanded 4 bits -> float4 (warp shuffle + a 16-entry float4 lookup table in
-//      shared memory) into a 4 KB staging tile in shared memory, 512 contiguous bytes per STS.128;
-//   3. one lane pushes the tile with cp.async.bulk.global.shared::cta (1-D TMA bulk store); tiles are
-//      double-buffered per warp, so assembling tile t+1 overlaps the store of tile t.
+// One env at a time per warp; the kernel body is a grid-stride loop over envs, so it runs either with one
+// env per warp (default: measured fastest -- the hardware CTA scheduler staggers the setup of new envs against
+// the streaming of the others; 6.73 TB/s) or with persistent warps (TC_WRITE_WAVES > 0 in the launcher;
+// 5.4-6.3 TB/s: the warps of an SM fall into lock step behind the TMA queue).  The env's output is one contiguous
+// run of P * 2d^2 floats starting at float index offsets[e] * 2d^2 (always even, so 8-byte aligned;
+// 16-byte aligned after peeling a 2-float "phantom" head that belongs to the previous env).  The run is
+// produced as a BIT stream first (bit t = output float t), one tile of 32*kWordsPerLane words at a time:
+//   1. lane L assembles words L, L+32, .. of the tile (two code paths, below);
+//   2. the words are expanded 4 bits -> float4 (warp shuffle + 8 integer ops) into a staging tile in
+//      shared memory, 512 contiguous bytes per STS.128;
+//   3. one lane pushes the tile with cp.async.bulk.global.shared::cta (1-D TMA bulk store).  Staging tiles
+//      are a per-warp ring (kStageBufs) that keeps rotating across envs; before a tile is refilled the warp
+//      waits (cp.async.bulk.wait_group.read) until the TMA engine has read it.
 // Measured on B200 (scripts/micro/write_peak*.cu): warp-wide st.global.v4 streams reach ~6.4 TB/s,
-// TMA bulk stores of 4-8 KB tiles ~7.0 TB/s (cudaMemset: 7.27 TB/s) -- hence the staging tile.
+// TMA bulk stores of 4-8 KB tiles ~7.0 TB/s (cudaMemset: 7.27 TB/s) -- hence the staging tile.  Tile size,
+// ring depth and warps per CTA were chosen by A/B timing (scripts/micro/build_variants.py, run_variants.sh):
+// 2 warps per CTA, 2 x 4 KB tiles per warp (10.3 KB of shared memory per warp at d=7, 22 warps per SM).
 //
 // Word assembly.  A perspective (m,i,j) shows plane c as a 2-D roll of a base plane (closed forms in
 // oracle/toric_oracle.py:perspective_view); with g = d/2, ia = (i-g)%d, rot = (j-g)%d, ra = (g-j)%d:
@@ -22,9 +28,10 @@
 // where S^T is the bit-transpose (built with d ballots).  With the m=1 base planes stored pre-permuted,
 // every case is "rows (a + r0) % d of base plane t = 2m+c, each rotated right by r1".
 //   * d <= 8 ("plane path"): a whole d x d plane fits one 64-bit word.  All 4*d*d rolled planes of the env
-//     are precomputed once with whole-plane shifts (row roll = 64-bit rotate by r0*d, column roll = two
-//     masked shifts) into shared memory; a stream word is then the funnel of the 2..5 consecutive planes
-//     that overlap it.
+//     are precomputed once (lane t*d+r0 builds the row-rolled plane, then d column rolls with compile-time
+//     masks and shifts) into shared memory; a stream word is then the funnel of the 2..5 consecutive planes
+//     that overlap it.  The env-independent decode of a candidate qubit q -> (plane index, position word)
+//     is a per-CTA table built once.
 //   * d > 8 ("row path"): lane L ORs the (<= ceil(31/d)+1) d-bit row fields that overlap its word, each
 //     read from row-doubled tables (w | w<<d, rows duplicated) so roll and rotation need no modulo.
 #pragma once
@@ -35,13 +42,13 @@
 namespace tc {
 
 #ifndef TC_TILE_WPL
-#define TC_TILE_WPL 2
+#define TC_TILE_WPL 1
 #endif
 #ifndef TC_STAGE_BUFS
-#define TC_STAGE_BUFS 1
+#define TC_STAGE_BUFS 2
 #endif
 #ifndef TC_WRITE_WARPS
-#define TC_WRITE_WARPS 4
+#define TC_WRITE_WARPS 2
 #endif
 constexpr int kWordsPerLane = TC_TILE_WPL;     // 32-bit stream words per lane and tile
 constexpr int kTileFloats = 1024 * kWordsPerLane;
@@ -60,10 +67,11 @@ struct PerspCfg {
   static constexpr int kPlanesPerWord = 1 + (31 + D * D - 1) / (D * D);
   static constexpr int kTabBytes = kPlane ? 4 * D * D * 8 : 4 * 2 * D * (int)sizeof(TabT);
   static constexpr int kPosBytes = ((kPMax + 2) * 2 + 15) & ~15;
-  static constexpr int kAuxBytes = kPlane ? (4 * 16 * 4 + 32 * 8) : 0;   // plane path: doubled base rows + row-rolled planes
+  static constexpr int kAuxBytes = kPlane ? 4 * 16 * 4 : 0;      // plane path: the 4 x d base rows, doubled
+  static constexpr int kCandBytes = kPlane ? ((2 * D * D * 8 + 127) & ~127) : 0;   // per-CTA candidate table
   // per-warp shared memory: [stage tiles][tab / planes][pos list][aux]
   static constexpr int kWarpBytes = kStageBufs * kTileBytes + ((kTabBytes + 15) & ~15) + kPosBytes + kAuxBytes;
-  static constexpr int kSmemBytes = kWarps * kWarpBytes;
+  static constexpr int kSmemBytes = kCandBytes + kWarps * kWarpBytes;
 };
 
 __device__ __forceinline__ void st_f2(float* p, float a, float b) {
@@ -99,210 +107,238 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int64_t e = (int64_t)blockIdx.x * Cfg::kWarps + warp;
-  if (e >= n) return;
-  unsigned char* wb = smem + warp * Cfg::kWarpBytes;
+  unsigned char* wb = smem + Cfg::kCandBytes + warp * Cfg::kWarpBytes;
   float* stage = reinterpret_cast<float*>(wb);
   unsigned char* tab_raw = wb + kStageBufs * kTileBytes;
   uint16_t* sp = reinterpret_cast<uint16_t*>(tab_raw + ((Cfg::kTabBytes + 15) & ~15));
   unsigned char* aux = reinterpret_cast<unsigned char*>(sp) + Cfg::kPosBytes;
+  uint32_t* pos32 = reinterpret_cast<uint32_t*>(pos);
 
-  uint32_t v = 0, pl = 0;
-  if (lane < D) {
-    v = __ldg(syn + e * 2 * D + lane);
-    pl = __ldg(syn + e * 2 * D + D + lane);
-  }
-  uint32_t m0, m1;
-  persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
-  const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
-  const int64_t off = block_off[e / epb] + (int64_t)local_off[e];
-  if (lane == 0) offsets[e] = off;
-  if (P == 0) return;
-  if (off + P > cap) {
-    if (lane == 0 && overflow) *overflow = 1;
-    return;
-  }
-
-  // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
-  // One candidate qubit q = m*d*d + i*d + j per lane and round; selected candidates are compacted in order
-  // with a ballot.  sp[k]: plane path = index of the c=0 rolled plane of perspective k (t=2m, r0, r1);
-  // row path = m | r0<<1 | r1<<6.   m=0: (r0, r1) = ((i-g)%d, (j-g)%d);  m=1: ((g-j)%d, (i-g)%d).
-  {
-    uint32_t* pos32 = reinterpret_cast<uint32_t*>(pos);
-    int kbase = 0;
-#pragma unroll 1
-    for (int q0 = 0; q0 < 2 * DD; q0 += 32) {
-      const int q = q0 + lane;
+  // ---- per-CTA candidate table (plane path): q = m*d*d + i*d + j -> {plane index | i<<16, position word} ----
+  // plane index = 2m*d*d + r0*d + r1 with (r0,r1) = ((i-g)%d, (j-g)%d) for m=0 and ((g-j)%d, (i-g)%d) for m=1
+  uint2* cand = reinterpret_cast<uint2*>(smem);
+  if constexpr (Cfg::kPlane) {
+    for (int q = threadIdx.x; q < 2 * DD; q += Cfg::kWarps * 32) {
       const int m = q >= DD ? 1 : 0;
       const int rem = q - m * DD;
       const int i = rem / D, j = rem - i * D;
-      const uint32_t r0m = __shfl_sync(kFull, m0, i & 31), r1m = __shfl_sync(kFull, m1, i & 31);
-      const bool sel = q < 2 * DD && (((m ? r1m : r0m) >> j) & 1u);
-      const uint32_t bal = __ballot_sync(kFull, sel);
-      if (sel) {
-        const int k = kbase + __popc(bal & ((1u << lane) - 1u));
-        const int ia = (i - G + D) % D;
-        const int r0 = m ? (G - j + D) % D : ia;
-        const int r1 = m ? ia : (j - G + D) % D;
-        sp[k] = Cfg::kPlane ? (uint16_t)(2 * m * DD + r0 * D + r1) : (uint16_t)(m | (r0 << 1) | (r1 << 6));
-        if (pos) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
-      }
-      kbase += __popc(bal);
+      const int ia = (i - G + D) % D;
+      const int r0 = m ? (G - j + D) % D : ia;
+      const int r1 = m ? ia : (j - G + D) % D;
+      cand[q] = make_uint2((uint32_t)(2 * m * DD + r0 * D + r1) | ((uint32_t)i << 16) | ((uint32_t)j << 24) |
+                               ((uint32_t)m << 31),
+                           (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16));
     }
+    __syncthreads();
   }
 
-  // ---- base tables: t = 2m + c; row a of table t (see header) ----
-  uint32_t tv = 0, tp = 0;
-#pragma unroll
-  for (int b = 0; b < D; ++b) {
-    const uint32_t bv = __ballot_sync(kFull, (v >> b) & 1u);
-    const uint32_t bp = __ballot_sync(kFull, (pl >> b) & 1u);
-    if (lane == b) { tv = bv; tp = bp; }
-  }
-  if constexpr (Cfg::kPlane) {
-    unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw);
-    uint32_t* rows = reinterpret_cast<uint32_t*>(aux);                         // [4][16]: rows doubled
-    unsigned long long* xs = reinterpret_cast<unsigned long long*>(aux + 4 * 16 * 4);   // [4*D] row-rolled planes
+  uint32_t ring = 0;                             // staging tiles pushed so far by this warp
+  const int64_t stride = (int64_t)gridDim.x * Cfg::kWarps;
+  for (int64_t e = (int64_t)blockIdx.x * Cfg::kWarps + warp; e < n; e += stride) {
+    uint32_t v = 0, pl = 0;
     if (lane < D) {
-      const int kv = (D - lane) % D, kp = D - 1 - lane;
-      rows[0 * 16 + lane] = v;
-      rows[0 * 16 + lane + D] = v;
-      rows[1 * 16 + lane] = pl;
-      rows[1 * 16 + lane + D] = pl;
-      rows[2 * 16 + kv] = tv & kRowMask;
-      rows[2 * 16 + kv + D] = tv & kRowMask;
-      rows[3 * 16 + kp] = tp & kRowMask;
-      rows[3 * 16 + kp + D] = tp & kRowMask;
+      v = __ldg(syn + e * 2 * D + lane);
+      pl = __ldg(syn + e * 2 * D + D + lane);
     }
-    __syncwarp();
-    if (lane < 4 * D) {                            // xs[t*D + r0][a] = T[t][(a + r0) % d]
-      const int t = lane / D, r0 = lane - t * D;
-      unsigned long long x = 0;
-#pragma unroll
-      for (int a = 0; a < D; ++a) x |= (unsigned long long)rows[t * 16 + a + r0] << (a * D);
-      xs[lane] = x;
+    int64_t off = 0;
+    if (lane == 0) off = __ldg(block_off + e / epb) + (int64_t)__ldg(local_off + e);
+    uint32_t m0, m1;
+    persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
+    const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
+    off = __shfl_sync(kFull, off, 0);
+    if (lane == 0) offsets[e] = off;
+    if (P == 0) continue;
+    if (off + P > cap) {
+      if (lane == 0 && overflow) *overflow = 1;
+      continue;
     }
-    __syncwarp();
-    constexpr unsigned long long kMaskDD = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
-    unsigned long long rep = 0;
-#pragma unroll
-    for (int a = 0; a < D; ++a) rep |= 1ull << (a * D);
+
+    // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
+    // One candidate qubit per lane and round; selected candidates are compacted in order with a ballot.
+    // sp[k]: plane path = index of the c=0 rolled plane of perspective k; row path = m | r0<<1 | r1<<6.
+    {
+      int kbase = 0;
 #pragma unroll 1
-    for (int idx = lane; idx < 4 * DD; idx += 32) {
-      const int tr = idx / D;                      // t*D + r0
-      const int r1 = idx - tr * D;
-      const unsigned long long x = xs[tr];
-      // column roll of every row at once: out[b] = w[(b + r1) % d]
-      const unsigned long long lo = rep * (unsigned long long)((1u << (D - r1)) - 1u);
-      planes[idx] = ((x >> r1) & lo) | ((x << (D - r1)) & (kMaskDD ^ lo));
-    }
-  } else {
-    TabT* tab = reinterpret_cast<TabT*>(tab_raw);
-    if (lane < D) {
-      const TabT dv = (TabT)v | ((TabT)v << D), dp = (TabT)pl | ((TabT)pl << D);
-      const TabT dtv = (TabT)tv | ((TabT)tv << D), dtp = (TabT)tp | ((TabT)tp << D);
-      tab[0 * 2 * D + lane] = dv;
-      tab[0 * 2 * D + lane + D] = dv;
-      tab[1 * 2 * D + lane] = dp;
-      tab[1 * 2 * D + lane + D] = dp;
-      const int kv = (D - lane) % D, kp = D - 1 - lane;
-      tab[2 * 2 * D + kv] = dtv;
-      tab[2 * 2 * D + kv + D] = dtv;
-      tab[3 * 2 * D + kp] = dtp;
-      tab[3 * 2 * D + kp + D] = dtp;
-    }
-  }
-  __syncwarp();
-
-  // ---- bit stream -> float tiles -> TMA bulk stores ----
-  const int64_t f_start = off * (int64_t)(2 * DD);
-  const int ph = (int)(f_start & 3);             // 0 or 2 phantom floats in front (owned by the previous env)
-  float* __restrict__ base = out + (f_start - ph);   // 16-byte aligned
-  const int F = P * 2 * DD;
-  const int L = F + ph;
-  const int nW = (L + 31) >> 5;
-  const int nT = (L + kTileFloats - 1) / kTileFloats;
-  const int L4 = L & ~3;                         // floats covered by whole float4s
-
-  auto assemble = [&](const int W) -> uint32_t {
-    uint32_t word = 0;
-    if (W < nW) {
-      if constexpr (Cfg::kPlane) {
-        const unsigned long long* planes = reinterpret_cast<const unsigned long long*>(tab_raw);
-        const int gg = 32 * W - ph + DD;         // shifted by one (empty) plane so that it is never negative
-        const int kk = gg / DD;
-        const int r = gg - kk * DD;              // first stream bit of the word inside plane kk-1
-#pragma unroll
-        for (int j = 0; j < Cfg::kPlanesPerWord; ++j) {
-          const int k = kk - 1 + j;              // plane k = perspective k>>1, syndrome plane k&1
-          const int sh = j * DD - r;
-          if (k >= 0 && k < 2 * P && sh < 32) {
-            const unsigned long long pv = planes[(int)sp[k >> 1] + (k & 1) * DD];
-            word |= (j == 0) ? (uint32_t)(pv >> r) : ((uint32_t)pv << sh);
+      for (int q0 = 0; q0 < 2 * DD; q0 += 32) {
+        const int q = q0 + lane;
+        if constexpr (Cfg::kPlane) {
+          const uint2 cd = cand[q < 2 * DD ? q : 0];
+          const uint32_t r0m = __shfl_sync(kFull, m0, (cd.x >> 16) & 31u);
+          const uint32_t r1m = __shfl_sync(kFull, m1, (cd.x >> 16) & 31u);
+          const bool sel = q < 2 * DD && ((((cd.x >> 31) ? r1m : r0m) >> ((cd.x >> 24) & 31u)) & 1u);
+          const uint32_t bal = __ballot_sync(kFull, sel);
+          if (sel) {
+            const int k = kbase + __popc(bal & ((1u << lane) - 1u));
+            sp[k] = (uint16_t)cd.x;
+            if (pos) pos32[off + k] = cd.y;
           }
-        }
-      } else {
-        const TabT* tab = reinterpret_cast<const TabT*>(tab_raw);
-        const int tbit0 = 32 * W - ph;           // stream bit held by bit 0 of this word
-        const int tb = tbit0 < 0 ? 0 : tbit0;
-        const int f = tb / D;                    // first row field touching the word
-        int p = f / (2 * D);
-        int rr = f - p * (2 * D);                // c * D + a
-        int sh = f * D - tbit0;                  // where that field starts inside the word (may be < 0)
-        uint32_t ent = sp[p];
-#pragma unroll
-        for (int it = 0; it < Cfg::kFields; ++it) {
-          if (sh < 32 && p < P) {
-            const int c = rr >= D ? 1 : 0;
-            const int a = rr - c * D;
-            const TabT tw = tab[(((ent & 1u) << 1) | c) * (2 * D) + a + ((ent >> 1) & 31u)];
-            const uint32_t fld = (uint32_t)(tw >> ((ent >> 6) & 31u)) & kRowMask;
-            word |= sh >= 0 ? (fld << sh) : (fld >> (-sh));
+          kbase += __popc(bal);
+        } else {
+          const int m = q >= DD ? 1 : 0;
+          const int rem = q - m * DD;
+          const int i = rem / D, j = rem - i * D;
+          const uint32_t r0m = __shfl_sync(kFull, m0, i & 31), r1m = __shfl_sync(kFull, m1, i & 31);
+          const bool sel = q < 2 * DD && (((m ? r1m : r0m) >> j) & 1u);
+          const uint32_t bal = __ballot_sync(kFull, sel);
+          if (sel) {
+            const int k = kbase + __popc(bal & ((1u << lane) - 1u));
+            int ia = i - G; if (ia < 0) ia += D;
+            int rj = m ? G - j : j - G; if (rj < 0) rj += D;
+            const int r0 = m ? rj : ia, r1 = m ? ia : rj;
+            sp[k] = (uint16_t)(m | (r0 << 1) | (r1 << 6));
+            if (pos) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
           }
-          sh += D;
-          if (++rr == 2 * D) {
-            rr = 0;
-            ++p;
-            ent = sp[p];
-          }
+          kbase += __popc(bal);
         }
       }
     }
-    return word;
-  };
 
-  for (int t = 0; t < nT; ++t) {
-    uint32_t word[kWordsPerLane];
+    // ---- base tables: t = 2m + c; row a of table t (see header) ----
+    uint32_t tv = 0, tp = 0;
 #pragma unroll
-    for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
-    float* st = stage + (t % kStageBufs) * kTileFloats;
-    if (t >= kStageBufs) {                       // the TMA engine must have read this buffer (tile t - kStageBufs)
-      if (lane == 0) {
-        if (kStageBufs == 1) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-        else asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+    for (int b = 0; b < D; ++b) {
+      const uint32_t bv = __ballot_sync(kFull, (v >> b) & 1u);
+      const uint32_t bp = __ballot_sync(kFull, (pl >> b) & 1u);
+      if (lane == b) { tv = bv; tp = bp; }
+    }
+    if constexpr (Cfg::kPlane) {
+      unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw);
+      uint32_t* rows = reinterpret_cast<uint32_t*>(aux);                         // [4][16]: rows doubled
+      if (lane < D) {
+        const int kv = (D - lane) % D, kp = D - 1 - lane;
+        rows[0 * 16 + lane] = v;
+        rows[0 * 16 + lane + D] = v;
+        rows[1 * 16 + lane] = pl;
+        rows[1 * 16 + lane + D] = pl;
+        rows[2 * 16 + kv] = tv & kRowMask;
+        rows[2 * 16 + kv + D] = tv & kRowMask;
+        rows[3 * 16 + kp] = tp & kRowMask;
+        rows[3 * 16 + kp + D] = tp & kRowMask;
       }
       __syncwarp();
-    }
-    float4* st4 = reinterpret_cast<float4*>(st);
+      if (lane < 4 * D) {
+        // lane = t*d + r0: row-rolled plane x[a] = T[t][(a + r0) % d], then the d column rolls
+        const int t = lane / D, r0 = lane - t * D;
+        unsigned long long x = 0;
 #pragma unroll
-    for (int u = 0; u < kWordsPerLane; ++u) {
+        for (int a = 0; a < D; ++a) x |= (unsigned long long)rows[t * 16 + a + r0] << (a * D);
+        constexpr unsigned long long kMaskDD = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
+        unsigned long long rep = 0;
 #pragma unroll
-      for (int s = 0; s < 8; ++s) {
-        const uint32_t wv = __shfl_sync(kFull, word[u], s * 4 + (lane >> 3));
-        st4[u * 256 + s * 32 + lane] = expand_nibble(wv >> ((lane & 7) * 4));
+        for (int a = 0; a < D; ++a) rep |= 1ull << (a * D);
+#pragma unroll
+        for (int r1 = 0; r1 < D; ++r1) {           // out[b] = w[(b + r1) % d] for every row at once
+          const unsigned long long lo = rep * (unsigned long long)((1u << (D - r1)) - 1u);
+          planes[lane * D + r1] = ((x >> r1) & lo) | ((x << (D - r1)) & (kMaskDD ^ lo));
+        }
+      }
+    } else {
+      TabT* tab = reinterpret_cast<TabT*>(tab_raw);
+      if (lane < D) {
+        const TabT dv = (TabT)v | ((TabT)v << D), dp = (TabT)pl | ((TabT)pl << D);
+        const TabT dtv = (TabT)tv | ((TabT)tv << D), dtp = (TabT)tp | ((TabT)tp << D);
+        tab[0 * 2 * D + lane] = dv;
+        tab[0 * 2 * D + lane + D] = dv;
+        tab[1 * 2 * D + lane] = dp;
+        tab[1 * 2 * D + lane + D] = dp;
+        const int kv = (D - lane) % D, kp = D - 1 - lane;
+        tab[2 * 2 * D + kv] = dtv;
+        tab[2 * 2 * D + kv + D] = dtv;
+        tab[3 * 2 * D + kp] = dtp;
+        tab[3 * 2 * D + kp + D] = dtp;
       }
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    if (lane == 0) {
-      const int f0 = t * kTileFloats;
-      const int lo = (t == 0 && ph) ? 4 : 0;
-      int hi = L4 - f0;
-      if (hi > kTileFloats) hi = kTileFloats;
-      if (t == 0 && ph) st_f2(base + 2, st[2], st[3]);                     // head: floats 2,3 of the first float4
-      if ((L & 3) && t == nT - 1) st_f2(base + L - 2, st[L - 2 - f0], st[L - 1 - f0]);   // tail half float4
-      if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * 4);
+
+    // ---- bit stream -> float tiles -> TMA bulk stores ----
+    const int64_t f_start = off * (int64_t)(2 * DD);
+    const int ph = (int)(f_start & 3);           // 0 or 2 phantom floats in front (owned by the previous env)
+    float* __restrict__ base = out + (f_start - ph);   // 16-byte aligned
+    const int F = P * 2 * DD;
+    const int L = F + ph;
+    const int nW = (L + 31) >> 5;
+    const int nT = (L + kTileFloats - 1) / kTileFloats;
+    const int L4 = L & ~3;                       // floats covered by whole float4s
+
+    auto assemble = [&](const int W) -> uint32_t {
+      uint32_t word = 0;
+      if (W < nW) {
+        if constexpr (Cfg::kPlane) {
+          const unsigned long long* planes = reinterpret_cast<const unsigned long long*>(tab_raw);
+          const int gg = 32 * W - ph + DD;       // shifted by one (empty) plane so that it is never negative
+          const int kk = gg / DD;
+          const int r = gg - kk * DD;            // first stream bit of the word inside plane kk-1
+#pragma unroll
+          for (int j = 0; j < Cfg::kPlanesPerWord; ++j) {
+            const int k = kk - 1 + j;            // plane k = perspective k>>1, syndrome plane k&1
+            const int sh = j * DD - r;
+            if (k >= 0 && k < 2 * P && sh < 32) {
+              const unsigned long long pv = planes[(int)sp[k >> 1] + (k & 1) * DD];
+              word |= (j == 0) ? (uint32_t)(pv >> r) : ((uint32_t)pv << sh);
+            }
+          }
+        } else {
+          const TabT* tab = reinterpret_cast<const TabT*>(tab_raw);
+          const int tbit0 = 32 * W - ph;         // stream bit held by bit 0 of this word
+          const int tb = tbit0 < 0 ? 0 : tbit0;
+          const int f = tb / D;                  // first row field touching the word
+          int p = f / (2 * D);
+          int rr = f - p * (2 * D);              // c * D + a
+          int sh = f * D - tbit0;                // where that field starts inside the word (may be < 0)
+          uint32_t ent = sp[p];
+#pragma unroll
+          for (int it = 0; it < Cfg::kFields; ++it) {
+            if (sh < 32 && p < P) {
+              const int c = rr >= D ? 1 : 0;
+              const int a = rr - c * D;
+              const TabT tw = tab[(((ent & 1u) << 1) | c) * (2 * D) + a + ((ent >> 1) & 31u)];
+              const uint32_t fld = (uint32_t)(tw >> ((ent >> 6) & 31u)) & kRowMask;
+              word |= sh >= 0 ? (fld << sh) : (fld >> (-sh));
+            }
+            sh += D;
+            if (++rr == 2 * D) {
+              rr = 0;
+              ++p;
+              ent = sp[p];
+            }
+          }
+        }
+      }
+      return word;
+    };
+
+    for (int t = 0; t < nT; ++t, ++ring) {
+      uint32_t word[kWordsPerLane];
+#pragma unroll
+      for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
+      float* st = stage + (ring % kStageBufs) * kTileFloats;
+      if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
+        __syncwarp();
+      }
+      float4* st4 = reinterpret_cast<float4*>(st);
+#pragma unroll
+      for (int u = 0; u < kWordsPerLane; ++u) {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          const uint32_t wv = __shfl_sync(kFull, word[u], s * 4 + (lane >> 3));
+          st4[u * 256 + s * 32 + lane] = expand_nibble(wv >> ((lane & 7) * 4));
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        const int f0 = t * kTileFloats;
+        const int lo = (t == 0 && ph) ? 4 : 0;
+        int hi = L4 - f0;
+        if (hi > kTileFloats) hi = kTileFloats;
+        if (t == 0 && ph) st_f2(base + 2, st[2], st[3]);                   // head: floats 2,3 of the first float4
+        if ((L & 3) && t == nT - 1) st_f2(base + L - 2, st[L - 2 - f0], st[L - 1 - f0]);   // tail half float4
+        if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * 4);
+        else asm volatile("cp.async.bulk.commit_group;" ::: "memory");     // keep one group per tile
+      }
     }
+    __syncwarp();
   }
   if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }

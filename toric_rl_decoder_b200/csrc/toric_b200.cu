@@ -404,18 +404,32 @@ inline Workspace carve(void* ws, int d, int64_t n) {
   return w;
 }
 
+// persistent grid: one CTA slot per (SM x resident CTAs), capped by the number of envs
 template <int D>
 void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
                   int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
   using Cfg = PerspCfg<D>;
   constexpr int WPB = Cfg::kWarps;
-  static bool configured = false;                 // opt in to > 48 KB of dynamic shared memory once per size
-  if (!configured) {
+  static int slots[64] = {0};                     // per device: SMs x resident CTAs of this instantiation
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (slots[dev] == 0) {
     cudaFuncSetAttribute(persp_write_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-    configured = true;
+    int sms = 148, occ = 1;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persp_write_kernel<D>, WPB * 32, Cfg::kSmemBytes);
+    slots[dev] = sms * (occ > 0 ? occ : 1);
   }
-  persp_write_kernel<D><<<grid_for(n, WPB), WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb,
-                                                                           out, pos, offsets, overflow, cap, n);
+  // TC_WRITE_WAVES: CTAs per resident slot.  0 = one env per warp (the hardware CTA scheduler staggers the
+  // env setups against the streaming of the others); k > 0 = persistent warps walking ~n/(slots*k*WPB) envs.
+#ifndef TC_WRITE_WAVES
+#define TC_WRITE_WAVES 0
+#endif
+  unsigned grid = grid_for(n, WPB);
+  if (TC_WRITE_WAVES > 0 && grid > (unsigned)slots[dev] * TC_WRITE_WAVES) grid = (unsigned)slots[dev] * TC_WRITE_WAVES;
+  persp_write_kernel<D><<<grid, WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb, out, pos,
+                                                                offsets, overflow, cap, n);
 }
 
 int write_dispatch(int d, const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
