@@ -286,12 +286,16 @@ def run_b200(a):
 
 
 def run_e2e(a, eng, dev, dist, barrier, world):
-    """Same metric through the host-facing call: every step copies that step's actions (n,4) int32 from
-    pinned host memory, runs the fused actor step, and reads rewards, terminals, perspective counts and
-    the new states (uint8 n,2,d,d) back to pinned host memory.  The perspective tensor stays on the
-    device, where the reference also puts it (`.to(device)`, src/numba/util_actor.py:39)."""
+    """Same metric through the host-facing call (toric_rl_decoder_b200.HostActorPipeline): every step copies
+    that step's actions (n,4) int32 from pinned host memory, runs the fused actor step, and reads rewards,
+    terminals, perspective counts and the new states (uint8 n,2,d,d) back to pinned host memory.  Uploads
+    and downloads run on their own streams with up to three steps in flight; every step's results are read on
+    the host inside the timed region.
+    The perspective tensor stays on the device, where the reference also puts it (`.to(device)`,
+    src/numba/util_actor.py:39)."""
     import numpy as np
     import torch
+    from toric_rl_decoder_b200 import HostActorPipeline, sharding
     d, n = a.d, a.envs
     rng = np.random.default_rng(a.seed + 17)
     n_buf = 8
@@ -300,40 +304,37 @@ def run_e2e(a, eng, dev, dist, barrier, world):
         arr = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)],
                        axis=1).astype(np.int32)
         host_actions.append(torch.from_numpy(arr).pin_memory())
-    h_reward = torch.empty(n, dtype=torch.float32).pin_memory()
-    h_term = torch.empty(n, dtype=torch.uint8).pin_memory()
-    h_counts = torch.empty(n, dtype=torch.int32).pin_memory()
-    h_state = torch.empty((n, 2, d, d), dtype=torch.uint8).pin_memory()
-    h2d = host_actions[0].numel() * 4
-    d2h = h_reward.numel() * 4 + h_term.numel() + h_counts.numel() * 4 + h_state.numel()
+    depth = 3
+    pipe = HostActorPipeline(eng, depth=depth)
+    checksum = 0.0
 
-    def one(k):
-        eng.actor_step(actions=host_actions[k % n_buf], auto_reset=True)
-        st = eng.get_state()
-        h_reward.copy_(eng.reward, non_blocking=True)
-        h_term.copy_(eng.terminal, non_blocking=True)
-        h_counts.copy_(eng.counts, non_blocking=True)
-        h_state.copy_(st, non_blocking=True)
-        torch.cuda.current_stream().synchronize()     # the caller consumes the results before the next step
+    def run(steps):
+        nonlocal checksum
+        for k in range(steps):
+            if pipe.submitted - pipe.collected >= depth:
+                res = pipe.collect()                    # the oldest step in flight is in host memory now
+                checksum += float(res["reward"][0]) + float(res["states"][0, 0, 0, 0])
+            pipe.submit(host_actions[k % n_buf], auto_reset=True)
+        while pipe.collected < pipe.submitted:
+            res = pipe.collect()
+            checksum += float(res["reward"][0])
 
-    for k in range(max(3, a.warmup)):
-        one(k)
+    run(max(3, a.warmup))
     barrier()
     c0 = eng.counters.clone()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    for k in range(a.steps):
-        one(k)
+    run(a.steps)
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
-    from toric_rl_decoder_b200 import sharding
     ms = sharding.max_over_ranks(ms, dev)
     dc = eng.counters - c0
-    return {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "ms_per_step": ms / a.steps,
+    return {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
+            "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
             "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
-            "call": "ToricEngine.actor_step(host actions) + host read of reward/terminal/counts/states",
+            "call": "HostActorPipeline.submit(pinned host actions) / collect() -> host reward, terminal, counts, "
+                    "states; uploads and downloads on their own streams, up to 3 steps in flight",
             "policy": "host-supplied uniformly random qubit + Pauli"}
 
 

@@ -212,3 +212,32 @@ def test_full_size_properties(pkg):
     before = eng.syn.clone()
     eng.syndrome()
     assert torch.equal(before, eng.syn)
+
+
+def test_host_pipeline_matches_oracle(pkg):
+    """HostActorPipeline (pinned host actions in, host results out, two steps in flight) == the numpy oracle."""
+    d, n, steps = 7, 300, 12
+    eng = pkg.ToricEngine(d, n, seed=5, p_error=0.1, max_steps=1000)
+    eng.reset()
+    q = eng.get_qubits().cpu().numpy().astype(np.int64)
+    s = eng.get_state().cpu().numpy().astype(np.int64)
+    rng = np.random.default_rng(0)
+    acts = [np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)],
+                     axis=1).astype(np.int32) for _ in range(steps)]
+    pinned = [torch.from_numpy(a).pin_memory() for a in acts]
+    pipe = pkg.HostActorPipeline(eng, depth=2)
+    got = []
+    for k in range(steps):
+        pipe.submit(pinned[k], auto_reset=False)
+        if k > 0:
+            r = pipe.collect()
+            got.append({key: np.array(val) for key, val in r.items()})
+    r = pipe.collect()
+    got.append({key: np.array(val) for key, val in r.items()})
+    for k in range(steps):
+        for e in range(n):
+            q[e], s[e], rew, term = O.step(q[e], s[e], acts[k][e])
+            assert got[k]["reward"][e] == rew and bool(got[k]["terminal"][e]) == term
+        assert (got[k]["states"] == s).all()
+        _, _, counts, _ = O.perspectives_batch(s)
+        assert (got[k]["counts"] == counts).all()

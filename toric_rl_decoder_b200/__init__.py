@@ -12,3 +12,4 @@ from .perspectives import (Perspective, generatePerspective, generatePerspective
                            generatePerspectiveOptimized)
 from .policy import (computePrioritiesParallel, generateTransitionParallel, predictMaxOptimized,  # noqa: F401
                      selectAction, selectActionBatch, select_action_device, transitions_device)
+from .hostpipe import HostActorPipeline  # noqa: F401

@@ -184,12 +184,16 @@ class ToricEngine:
                                             self.workspace.numel(), self.d, n, _stream()), "tc_perspectives")
 
     def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
-                   freeze_done=False):
+                   freeze_done=False, actions_buffer=None):
         """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
-        self.actions itself (e.g. filled by select_action) skips the copy.  freeze_done leaves envs whose
+        self.actions itself (e.g. filled by select_action) skips the copy; actions_buffer (device int32
+        (n,4), 16-byte aligned) is read in place instead of self.actions.  freeze_done leaves envs whose
         syndrome is already trivial untouched (batched evaluation)."""
         flags = (ACTOR_AUTO_RESET if auto_reset else 0) | (ACTOR_FREEZE_DONE if freeze_done else 0)
-        if actions is None:
+        act_buf = self.actions
+        if actions_buffer is not None:
+            act_buf = actions_buffer
+        elif actions is None:
             flags |= ACTOR_RANDOM_ACTIONS
         elif actions is not self.actions:
             self.actions.copy_(torch.as_tensor(actions).to(torch.int32), non_blocking=True)
@@ -200,7 +204,7 @@ class ToricEngine:
         self._last_syn = self.syn
         self.overflow.zero_()
         _lib.check(self.lib.tc_actor_step(
-            _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(self.actions),
+            _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
             _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
             _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
             int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(self.counts),

@@ -1,0 +1,105 @@
+"""Host-buffer front end of the fused actor step: the reference-facing call with HOST arrays.
+
+The reference's actor loop hands `EnvSet.step` a host array of actions and reads rewards, terminals and the
+new states back as host arrays (src/Actor_mp.py:116-125, src/EnvSet.py:38-47).  `HostActorPipeline` keeps
+that contract on the GPU engine and overlaps the PCIe copies with the kernels:
+
+    h2d stream:      actions(k+1)
+    compute stream:  actor_step(k) | snapshot(k) | actor_step(k+1) | snapshot(k+1) ...
+    d2h stream:                                  | results(k)                      | results(k+1)
+
+(two copy streams: on a single one the upload of step k+1 would queue behind the download of step k, which
+waits for compute k, and nothing would overlap)
+
+Per slot (ring of `depth`): a device action buffer, one contiguous device staging block
+[reward f32 | counts i32 | terminal u8 | states u8 (n,2,d,d)] and its pinned host twin, so every step moves
+exactly one H2D and one D2H memcpy.  The perspective tensor stays on the device, where the reference also
+puts it (`.to(device)`, src/numba/util_actor.py:39).
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .engine import _ptr
+
+
+class HostActorPipeline:
+    def __init__(self, engine, depth=2):
+        self.eng = engine
+        self.depth = int(depth)
+        n, d = engine.n, engine.d
+        dev = engine.device
+        self.h2d_stream = torch.cuda.Stream(device=dev)
+        self.d2h_stream = torch.cuda.Stream(device=dev)
+        self.o_reward = 0
+        self.o_counts = 4 * n
+        self.o_term = 8 * n
+        self.o_state = (9 * n + 15) & ~15
+        self.nbytes = self.o_state + n * 2 * d * d
+        self.h2d_bytes = n * 16
+        self.d2h_bytes = self.nbytes
+        self.slots = []
+        for _ in range(self.depth):
+            slot = {
+                "d_actions": torch.empty((n, 4), dtype=torch.int32, device=dev),
+                "d_stage": torch.empty(self.nbytes, dtype=torch.uint8, device=dev),
+                "h_stage": torch.empty(self.nbytes, dtype=torch.uint8).pin_memory(),
+                "ev_actions": torch.cuda.Event(), "ev_compute": torch.cuda.Event(), "ev_result": torch.cuda.Event(),
+                "busy": False,
+            }
+            hs = slot["h_stage"].numpy()
+            slot["views"] = {
+                "reward": hs[self.o_reward:self.o_reward + 4 * n].view(np.float32),
+                "counts": hs[self.o_counts:self.o_counts + 4 * n].view(np.int32),
+                "terminal": hs[self.o_term:self.o_term + n].view(np.bool_),
+                "states": hs[self.o_state:self.o_state + n * 2 * d * d].reshape(n, 2, d, d),
+            }
+            ds = slot["d_stage"]
+            slot["d_reward"] = ds[self.o_reward:self.o_reward + 4 * n].view(torch.float32)
+            slot["d_counts"] = ds[self.o_counts:self.o_counts + 4 * n].view(torch.int32)
+            slot["d_term"] = ds[self.o_term:self.o_term + n]
+            slot["d_state"] = ds[self.o_state:self.o_state + n * 2 * d * d]
+            self.slots.append(slot)
+        self.submitted = 0
+        self.collected = 0
+
+    def submit(self, actions_host, auto_reset=True):
+        """Enqueue one step.  actions_host: pinned int32 tensor (n,4).  Never blocks the host unless the
+        ring is full (then the oldest result must be collected first)."""
+        if self.submitted - self.collected >= self.depth:
+            raise RuntimeError("pipeline full: collect() before submitting again")
+        eng = self.eng
+        slot = self.slots[self.submitted % self.depth]
+        compute = torch.cuda.current_stream(eng.device)
+        with torch.cuda.stream(self.h2d_stream):
+            slot["d_actions"].copy_(actions_host, non_blocking=True)
+            slot["ev_actions"].record(self.h2d_stream)
+        compute.wait_event(slot["ev_actions"])
+        eng.actor_step(auto_reset=auto_reset, actions_buffer=slot["d_actions"])
+        slot["d_reward"].copy_(eng.reward, non_blocking=True)
+        slot["d_counts"].copy_(eng.counts, non_blocking=True)
+        slot["d_term"].copy_(eng.terminal, non_blocking=True)
+        _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
+                                           compute.cuda_stream), "tc_unpack_state")
+        slot["ev_compute"].record(compute)
+        with torch.cuda.stream(self.d2h_stream):
+            self.d2h_stream.wait_event(slot["ev_compute"])
+            slot["h_stage"].copy_(slot["d_stage"], non_blocking=True)
+            slot["ev_result"].record(self.d2h_stream)
+        self.submitted += 1
+
+    def collect(self):
+        """Block until the oldest outstanding step's results are in host memory; returns numpy views
+        {reward f32 (n,), counts i32 (n,), terminal bool (n,), states u8 (n,2,d,d)} valid until the slot is
+        reused (depth submits later)."""
+        if self.collected >= self.submitted:
+            raise RuntimeError("nothing to collect")
+        slot = self.slots[self.collected % self.depth]
+        slot["ev_result"].synchronize()
+        self.collected += 1
+        return slot["views"]
+
+    def step(self, actions_host, auto_reset=True):
+        """Unpipelined convenience form: submit + collect."""
+        self.submit(actions_host, auto_reset=auto_reset)
+        return self.collect()
