@@ -183,6 +183,13 @@ class ToricEngine:
                                             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace),
                                             self.workspace.numel(), self.d, n, _stream()), "tc_perspectives")
 
+    def perspectives_count(self, syn=None, n=None):
+        """Count + scan only (tc_persp_count): fills counts and offsets[n] = total, writes no perspectives."""
+        syn = self.syn if syn is None else syn
+        n = syn.shape[0] if n is None else n
+        _lib.check(self.lib.tc_persp_count(_ptr(syn), _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace),
+                                           self.workspace.numel(), self.d, n, _stream()), "tc_persp_count")
+
     def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
                    freeze_done=False, actions_buffer=None):
         """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
