@@ -84,6 +84,10 @@ __device__ __forceinline__ uint32_t rotr_d(uint32_t w, int d) {
   return ((w >> 1) | (w << (d - 1))) & row_mask(d);
 }
 
+// periodic neighbours without an integer division (d is a runtime value in the state kernels)
+__device__ __forceinline__ int wrap_inc(int x, int d) { return x + 1 >= d ? x + 1 - d : x + 1; }
+__device__ __forceinline__ int wrap_dec(int x, int d) { return x == 0 ? d - 1 : x - 1; }
+
 template <int G>
 __device__ __forceinline__ uint32_t group_mask() {
   if (G == 32) return 0xffffffffu;
@@ -134,8 +138,8 @@ struct Rows {
 //   Pl[i,j] = x0[i,j] ^ x0[i,j+1] ^ x1[i,j] ^ x1[i+1,j]
 template <int G>
 __device__ __forceinline__ void syndrome_rows(uint32_t gmask, int d, int r, Rows& s) {
-  const int up = (r + d - 1) % d;     // row i-1 (lanes >= d read a valid lane, result discarded)
-  const int dn = (r + 1) % d;         // row i+1
+  const int up = wrap_dec(r, d);     // row i-1 (lanes >= d read a valid lane, result discarded)
+  const int dn = wrap_inc(r, d);        // row i+1
   const uint32_t z0_up = gshfl<G>(gmask, s.z0, up);
   const uint32_t x1_dn = gshfl<G>(gmask, s.x1, dn);
   if (r < d) {
@@ -153,8 +157,8 @@ __device__ __forceinline__ void syndrome_rows(uint32_t gmask, int d, int r, Rows
 template <int G>
 __device__ __forceinline__ void persp_masks(uint32_t gmask, int d, int r, uint32_t v, uint32_t pl,
                                             uint32_t& m0, uint32_t& m1) {
-  const uint32_t v_dn = gshfl<G>(gmask, v, (r + 1) % d);
-  const uint32_t pl_up = gshfl<G>(gmask, pl, (r + d - 1) % d);
+  const uint32_t v_dn = gshfl<G>(gmask, v, wrap_inc(r, d));
+  const uint32_t pl_up = gshfl<G>(gmask, pl, wrap_dec(r, d));
   if (r < d) {
     m0 = v | v_dn | pl | rotl_d(pl, d);
     m1 = v | rotr_d(v, d) | pl | pl_up;

@@ -65,16 +65,16 @@ __device__ __forceinline__ bool apply_action(int d, int r, int m, int i, int j, 
   const uint32_t bit = 1u << j;
   if (m == 0) {
     if (r == i) {
-      if (xp) { s.x0 ^= bit; s.pl ^= bit | (1u << ((j + d - 1) % d)); }
+      if (xp) { s.x0 ^= bit; s.pl ^= bit | (1u << wrap_dec(j, d)); }
       if (zp) { s.z0 ^= bit; s.v ^= bit; }
     }
-    if (zp && r == (i + 1) % d) s.v ^= bit;
+    if (zp && r == wrap_inc(i, d)) s.v ^= bit;
   } else {
     if (r == i) {
       if (xp) { s.x1 ^= bit; s.pl ^= bit; }
-      if (zp) { s.z1 ^= bit; s.v ^= bit | (1u << ((j + 1) % d)); }
+      if (zp) { s.z1 ^= bit; s.v ^= bit | (1u << wrap_inc(j, d)); }
     }
-    if (xp && r == (i + d - 1) % d) s.pl ^= bit;
+    if (xp && r == wrap_dec(i, d)) s.pl ^= bit;
   }
   return true;
 }
@@ -177,6 +177,21 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
   st.nz = __popc(s.z0 & ~s.x0) + __popc(s.z1 & ~s.x1);
 }
 
+// position of the n-th (0-based) set bit of m; m must have more than n bits set
+__device__ __forceinline__ int nth_set_bit(uint32_t m, int n) {
+  int pos = 0;
+#pragma unroll
+  for (int w = 16; w >= 1; w >>= 1) {
+    const int c = __popc(m & ((1u << w) - 1u));
+    if (n >= c) {
+      n -= c;
+      pos += w;
+      m >>= w;
+    }
+  }
+  return pos;
+}
+
 // Uniform pick from the env's perspective list x {X,Y,Z} (the random branch of
 // _selectActionBatch_prime, src/numba/util_actor.py:96-98): k = mulhi(u0, P) indexes the list in
 // reference order (matrix 0 row-major, then matrix 1), op = 1 + mulhi(u1, 3).
@@ -194,8 +209,8 @@ __device__ __forceinline__ void random_action(uint32_t gmask, int d, int r, uint
   int packed = 0;   // m<<16 | i<<8 | j ; stays 0 -> (0,0,0) when the list is empty
   if (P > 0) {
     const int k = (int)mulhi32(rnd.x, (uint32_t)P);
-    if (k >= b0 && k < b0 + c0) packed = (0 << 16) | (r << 8) | (int)__fns(m0, 0, k - b0 + 1);
-    if (k >= b1 && k < b1 + c1) packed = (1 << 16) | (r << 8) | (int)__fns(m1, 0, k - b1 + 1);
+    const bool in0 = k >= b0 && k < b0 + c0, in1 = k >= b1 && k < b1 + c1;
+    if (in0 || in1) packed = ((in1 ? 1 : 0) << 16) | (r << 8) | nth_set_bit(in1 ? m1 : m0, in1 ? k - b1 : k - b0);
   }
   // exactly one lane holds the pick: OR-reduce
 #pragma unroll

@@ -269,7 +269,7 @@ struct ActorArgs {
 };
 
 template <int G>
-__global__ void __launch_bounds__(kThreads) actor_step_kernel(const ActorArgs a) {
+__global__ void __launch_bounds__(kThreads, 4) actor_step_kernel(const ActorArgs a) {
   __shared__ unsigned int s_ctr[kNumCounters];
   if (threadIdx.x < kNumCounters) s_ctr[threadIdx.x] = 0;
   __syncthreads();
