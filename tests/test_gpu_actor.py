@@ -180,10 +180,12 @@ def _torch_reference_perspectives(state, pos, env_of, d):
     return torch.stack((out0, out1), dim=1).float()
 
 
-def test_full_size_properties(pkg):
-    """BASELINE config 2 size (d=7, 65536 envs): after a few fused steps, every perspective equals an
-    independent torch gather; counts equal the popcount of the selection masks; offsets are their scan."""
-    d, n = 7, 65536
+@pytest.mark.parametrize("d,n", ((7, 65536), (5, 30000), (8, 4096), (4, 8192), (3, 5000), (9, 8192), (15, 4096),
+                                 (25, 1024), (32, 300)))
+def test_full_size_properties(pkg, d, n):
+    """BASELINE configs[1] size (d=7, 65536 envs) and the other lattice sizes / both writer code paths: after a
+    few fused steps, every perspective equals an independent torch gather; counts equal the popcount of the
+    selection masks; offsets are their scan."""
     eng = pkg.ToricEngine(d, n, seed=1, p_error=0.1)
     eng.reset()
     for _ in range(5):
@@ -200,7 +202,7 @@ def test_full_size_properties(pkg):
     assert (nz[:, 1:].to(torch.uint8) == pos[:, :3]).all()
     total = persp.shape[0]
     assert total == nz.shape[0]
-    chunk = 1 << 20
+    chunk = max(1024, (1 << 26) // (d * d))
     for lo in range(0, total, chunk):
         hi = min(total, lo + chunk)
         ref = _torch_reference_perspectives(state, pos[lo:hi], nz[lo:hi, 0], d)
