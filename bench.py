@@ -38,14 +38,17 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--cpu-envs", type=int, default=8192, help="envs in the bounded CPU sample")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--out-dtype", default="float32", choices=("float32", "bfloat16", "float16", "uint8"),
+                    help="element type of the perspective tensor; float32 = the reference's (headline)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
 
 def workload_name(a):
-    return ("d=%d p=%g %d envs/GPU random actions: step + auto-reset + perspectives (fp32)"
-            % (a.d, a.p, a.envs))
+    short = {"float32": "fp32", "bfloat16": "bf16", "float16": "fp16", "uint8": "u8"}[a.out_dtype]
+    return ("d=%d p=%g %d envs/GPU random actions: step + auto-reset + perspectives (%s)"
+            % (a.d, a.p, a.envs, short))
 
 
 def b_alg(d, n_envs, sum_p, s=4):
@@ -54,9 +57,9 @@ def b_alg(d, n_envs, sum_p, s=4):
     return n_envs * per_env + sum_p * (2 * d * d * s + 4)
 
 
-def write_kernel_bytes(d, n_envs, sum_p):
+def write_kernel_bytes(d, n_envs, sum_p, s=4):
     """Algorithmic bytes of one persp_write_kernel launch: perspectives + positions out, syndrome + offsets."""
-    return sum_p * (2 * d * d * 4 + 4) + n_envs * (((2 * d * d + 7) // 8) + 8)
+    return sum_p * (2 * d * d * s + 4) + n_envs * (((2 * d * d + 7) // 8) + 8)
 
 
 # ----------------------------------------------------------------------------------------------
@@ -203,7 +206,10 @@ def run_b200(a):
     dev = torch.device("cuda", local)
     d, n = a.d, a.envs
 
-    eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p)   # envs shard by rank
+    out_dtype = getattr(torch, a.out_dtype)
+    esz = torch.empty((), dtype=out_dtype).element_size()
+    eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p,
+                          out_dtype=out_dtype)                                              # envs shard by rank
     eng.ensure_capacity(eng.worst_case_capacity())
     eng.reset()
 
@@ -244,14 +250,14 @@ def run_b200(a):
     p_bar = sum_p_local / float(n * a.steps)
 
     peak, peak_src = load_peaks()
-    wbytes = write_kernel_bytes(d, n, sum_p_local / a.steps)
+    wbytes = write_kernel_bytes(d, n, sum_p_local / a.steps, esz)
     achieved = wbytes / (write_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "persp_write_kernel<%d>" % d, "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "persp_write_kernel<%d,%s>" % (d, a.out_dtype), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
-                "step_achieved": b_alg(d, n, sum_p_local / a.steps) / (ms / a.steps * 1e-3) / 1e9}
+                "step_achieved": b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9}
     tr = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tr):
+    if os.path.exists(tr) and a.out_dtype == "float32" and d == 7:
         try:
             roofline["traffic"] = json.load(open(tr)).get("persp_write_bytes_per_launch")
         except Exception:
@@ -270,13 +276,15 @@ def run_b200(a):
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-                "vs_baseline": None, "dtype": "u32 bit planes -> f32", "data": "synthetic",
+                "vs_baseline": None, "dtype": "u32 bit planes -> %s" % {"float32": "f32", "bfloat16": "bf16",
+                                                                        "float16": "f16", "uint8": "u8"}[a.out_dtype],
+                "data": "synthetic",
                 "config": {"workload": workload_name(a), "d": d, "p_error": a.p, "envs_per_gpu": n,
                            "global_envs": n * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
-                           "mean_perspectives_per_env": p_bar, "out_dtype": "float32",
+                           "mean_perspectives_per_env": p_bar, "out_dtype": a.out_dtype,
                            "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
                                  % (wbytes / 1e9),
-                           "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps) / n},
+                           "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": 3 * a.steps,
                 "clocks": clk.summary(),
                 "counters": {k: c[k] for k in ("episodes", "solved", "ground_kept", "timeouts", "perspectives")}}

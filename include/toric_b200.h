@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 2
+#define TC_ABI_VERSION 3
 #define TC_NUM_COUNTERS 16
 
 /* status bits written per env */
@@ -48,6 +48,8 @@ extern "C" {
 /* element types of tc_transitions outputs */
 #define TC_DTYPE_F32 0
 #define TC_DTYPE_U8 1
+#define TC_DTYPE_BF16 2 /* tc_persp_write_as / tc_perspectives_as only */
+#define TC_DTYPE_F16 3
 
 int tc_abi_version(void);
 
@@ -103,6 +105,19 @@ int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void*
                    size_t workspace_bytes, int d, int64_t n, void* stream);
 int tc_persp_write(const uint32_t* syn, float* out, uint8_t* pos, int64_t* offsets, int32_t* overflow,
                    int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n, void* stream);
+
+/* tc_persp_write / tc_perspectives with the element type of the network-input tensor chosen by the caller
+ * ("T* out, int out_dtype").  The reference casts to float32
+ * (`.type('torch.Tensor')`, src/numba/util_actor.py:39; src/util_actor.py:36); the values are 0/1, so
+ * TC_DTYPE_BF16 / TC_DTYPE_F16 / TC_DTYPE_U8 carry the same tensor exactly at 2 / 2 / 1 bytes per element
+ * for a network run under bf16/fp16 autocast or with an integer input stage.  out: [cap][2][d][d] of that
+ * type, 16-byte aligned. */
+int tc_persp_write_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* pos, int64_t* offsets,
+                      int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
+                      void* stream);
+int tc_perspectives_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* pos, int32_t* counts,
+                       int64_t* offsets, int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes,
+                       int d, int64_t n, void* stream);
 
 /* One fused actor iteration over all envs (the loop body of src/Actor_mp.py:104-185 minus the
  * network): optional on-device random action, step, reward/terminal, episode bookkeeping with

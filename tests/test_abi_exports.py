@@ -26,7 +26,7 @@ def test_header_symbols_exported(lib_path):
     assert len(names) >= 14
     for n in names:
         assert hasattr(lib, n), "missing export %s" % n
-    assert lib.tc_abi_version() == 2
+    assert lib.tc_abi_version() == 3
 
 
 def test_binding_covers_header(lib_path):
@@ -44,6 +44,7 @@ def test_argument_validation_without_gpu(lib_path):
     assert lib.tc_workspace_bytes(33, 10, ctypes.byref(nbytes)) == -1
     assert lib.tc_syndrome(None, None, 7, 10, None) == -1
     assert lib.tc_step(None, None, None, None, None, None, 7, 10, None) == -1
+    assert lib.tc_persp_write_as(None, None, 0, None, None, None, 0, None, 0, 7, 10, None) == -1
 
 
 def test_no_cpu_fallback():

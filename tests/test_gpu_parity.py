@@ -201,3 +201,45 @@ def test_abi_argument_errors(pkg):
     assert rc == -2
     with pytest.raises(ValueError):
         pkg.ToricEngine(2, 4)
+
+
+@pytest.mark.parametrize("dtype", ("bfloat16", "float16", "uint8"))
+@pytest.mark.parametrize("d,n", ((3, 700), (4, 300), (5, 2000), (7, 4096), (8, 512), (9, 1024), (15, 256), (25, 64),
+                                 (32, 16)))
+def test_perspective_element_types(pkg, d, n, dtype):
+    """tc_persp_write_as: the bf16 / fp16 / u8 tensors carry exactly the float32 tensor's 0/1 values (all
+    head/tail alignments of the env runs occur: offsets are arbitrary), and nothing is written past the
+    last perspective."""
+    tdt = getattr(torch, dtype)
+    rng = np.random.default_rng(7 * d + n)
+    q = ((rng.random((n, 2, d, d)) < 0.06) * rng.integers(1, 4, (n, 2, d, d))).astype(np.uint8)
+    q[0] = 0
+    q[n // 2] = rng.integers(0, 4, (2, d, d))
+    ref = pkg.ToricEngine(d, n)
+    ref.set_qubits(q)
+    ref.perspectives()
+    p32, pos32, c32, off32 = ref.perspective_views()
+    eng = pkg.ToricEngine(d, n, out_dtype=tdt)
+    eng.set_qubits(q)
+    total = int(off32[-1].item())
+    eng.ensure_capacity(total + 3)
+    guard = 0x5a
+    eng.out.view(torch.uint8).fill_(guard)
+    eng.perspectives()
+    p, pos, c, off = eng.perspective_views()
+    assert p.dtype == tdt and p.shape == p32.shape
+    assert torch.equal(c, c32) and torch.equal(off, off32) and torch.equal(pos[:, :3], pos32[:, :3])
+    assert torch.equal(p.float(), p32)
+    assert (eng.out[total:].view(torch.uint8) == guard).all()
+    if n <= 1024:
+        op, opos, oc, ooff = O.perspectives_batch(O.syndrome(q))
+        assert (p.float().cpu().numpy() == op).all()
+    # fused actor step path with the same element type
+    e32 = pkg.ToricEngine(d, n, seed=3, p_error=0.1)
+    e16 = pkg.ToricEngine(d, n, seed=3, p_error=0.1, out_dtype=tdt)
+    for e in (e32, e16):
+        e.reset()
+        e.actor_step()
+        e.actor_step()
+    a, b = e32.perspective_views(), e16.perspective_views()
+    assert torch.equal(a[0], b[0].float()) and torch.equal(a[1], b[1]) and torch.equal(a[3], b[3])

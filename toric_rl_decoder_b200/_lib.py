@@ -26,6 +26,8 @@ SIGNATURES = {
     "tc_perspectives": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
     "tc_persp_count": [_vp, _vp, _vp, _vp, _sz, _i, _i64, _vp],
     "tc_persp_write": [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_persp_write_as": [_vp, _vp, _i, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_perspectives_as": [_vp, _vp, _i, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
     "tc_actor_pre": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
                      _vp, _vp, _vp, _sz, _i, _i64, _vp],
     "tc_actor_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
@@ -36,7 +38,7 @@ SIGNATURES = {
     "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],
 }
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 _lib = None
 
 

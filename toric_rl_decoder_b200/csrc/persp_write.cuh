@@ -50,10 +50,22 @@ namespace tc {
 #ifndef TC_WRITE_WARPS
 #define TC_WRITE_WARPS 2
 #endif
-constexpr int kWordsPerLane = TC_TILE_WPL;     // 32-bit stream words per lane and tile
-constexpr int kTileFloats = 1024 * kWordsPerLane;
-constexpr int kTileBytes = kTileFloats * 4;
+constexpr int kTileBytes = 4096 * TC_TILE_WPL; // staging tile: 32 lanes x TC_TILE_WPL stream words of float32 output
 constexpr int kStageBufs = TC_STAGE_BUFS;      // staging tiles per warp (1: wait for the TMA read before refill)
+
+// Output element types.  The stream is 0/1 valued, so every type is exact; float32 is the reference's
+// (`.type('torch.Tensor')`, src/numba/util_actor.py:39), the narrower ones feed a bf16/fp16-autocast or
+// integer-input network without a cast kernel.  OutT = float | uint16_t (bf16 / fp16, the bit pattern of 1.0
+// is a kernel argument) | uint8_t.  kE = elements per 16-byte chunk = stream bits per STS.128.
+template <typename OutT>
+struct OutCfg {
+  static constexpr int kB = (int)sizeof(OutT);
+  static constexpr int kE = 16 / kB;
+  static constexpr int kWordsPerLane = TC_TILE_WPL * 4 / kB;   // 32-bit stream words per lane and tile
+  static constexpr int kTileElems = 1024 * kWordsPerLane;      // = kTileBytes / kB
+  using PairT = typename std::conditional<kB == 4, float2,
+                                          typename std::conditional<kB == 2, uint32_t, uint16_t>::type>::type;
+};
 
 template <int D>
 struct PerspCfg {
@@ -74,30 +86,45 @@ struct PerspCfg {
   static constexpr int kSmemBytes = kCandBytes + kWarps * kWarpBytes;
 };
 
-__device__ __forceinline__ void st_f2(float* p, float a, float b) {
-  __stcs(reinterpret_cast<float2*>(p), make_float2(a, b));
-}
-
-__device__ __forceinline__ void bulk_store(float* gdst, const void* ssrc, int bytes) {
+__device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, int bytes) {
   const uint32_t sa = (uint32_t)__cvta_generic_to_shared(ssrc);
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(sa), "r"(bytes)
                : "memory");
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
-// 4 stream bits -> 4 floats: bit * 0x3f800000 (1.0f), with the bit still at its position in the nibble
-__device__ __forceinline__ float4 expand_nibble(uint32_t nib) {
-  return make_float4(__uint_as_float((nib & 1u) * 0x3f800000u), __uint_as_float((nib & 2u) * 0x1fc00000u),
-                     __uint_as_float((nib & 4u) * 0x0fe00000u), __uint_as_float((nib & 8u) * 0x07f00000u));
+// kE stream bits -> one 16-byte chunk of output elements
+template <typename OutT>
+__device__ __forceinline__ uint4 expand_chunk(uint32_t bits, uint32_t one16) {
+  if constexpr (sizeof(OutT) == 4) {
+    // 4 bits -> 4 floats: bit * 0x3f800000 (1.0f), with the bit still at its position in the nibble
+    return make_uint4((bits & 1u) * 0x3f800000u, (bits & 2u) * 0x1fc00000u, (bits & 4u) * 0x0fe00000u,
+                      (bits & 8u) * 0x07f00000u);
+  } else if constexpr (sizeof(OutT) == 2) {
+    // 8 bits -> 8 halves: two per 32-bit word, one16 = bit pattern of 1.0 (0x3f80 bf16, 0x3c00 fp16)
+    const uint32_t hi = one16 << 15;             // (x & 2) * hi puts 1.0 in the upper half
+    return make_uint4((bits & 1u) * one16 + (bits & 2u) * hi, ((bits >> 2) & 1u) * one16 + ((bits >> 2) & 2u) * hi,
+                      ((bits >> 4) & 1u) * one16 + ((bits >> 4) & 2u) * hi,
+                      ((bits >> 6) & 1u) * one16 + ((bits >> 6) & 2u) * hi);
+  } else {
+    // 16 bits -> 16 bytes: a nibble times 0x00204081 lands bit k at bit 8k (the four partial products do not overlap)
+    return make_uint4(((bits & 15u) * 0x00204081u) & 0x01010101u, (((bits >> 4) & 15u) * 0x00204081u) & 0x01010101u,
+                      (((bits >> 8) & 15u) * 0x00204081u) & 0x01010101u,
+                      (((bits >> 12) & 15u) * 0x00204081u) & 0x01010101u);
+  }
 }
 
-template <int D>
+template <int D, typename OutT>
 __global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
 persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
-                   const int64_t* __restrict__ block_off, int epb, float* __restrict__ out,
+                   const int64_t* __restrict__ block_off, int epb, OutT* __restrict__ out,
                    uint8_t* __restrict__ pos, int64_t* __restrict__ offsets, int32_t* __restrict__ overflow,
-                   int64_t cap, int64_t n) {
+                   int64_t cap, int64_t n, uint32_t one16) {
   using Cfg = PerspCfg<D>;
+  using OC = OutCfg<OutT>;
+  constexpr int kE = OC::kE;
+  constexpr int kWordsPerLane = OC::kWordsPerLane;
+  constexpr int kTileElems = OC::kTileElems;
   using TabT = typename Cfg::TabT;
   constexpr int G = D / 2;                       // grid_shift (src/Actor_mp.py:59)
   constexpr int DD = D * D;
@@ -108,7 +135,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   unsigned char* wb = smem + Cfg::kCandBytes + warp * Cfg::kWarpBytes;
-  float* stage = reinterpret_cast<float*>(wb);
+  OutT* stage = reinterpret_cast<OutT*>(wb);
   unsigned char* tab_raw = wb + kStageBufs * kTileBytes;
   uint16_t* sp = reinterpret_cast<uint16_t*>(tab_raw + ((Cfg::kTabBytes + 15) & ~15));
   unsigned char* aux = reinterpret_cast<unsigned char*>(sp) + Cfg::kPosBytes;
@@ -250,15 +277,15 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     }
     __syncwarp();
 
-    // ---- bit stream -> float tiles -> TMA bulk stores ----
+    // ---- bit stream -> output tiles -> TMA bulk stores ----
     const int64_t f_start = off * (int64_t)(2 * DD);
-    const int ph = (int)(f_start & 3);           // 0 or 2 phantom floats in front (owned by the previous env)
-    float* __restrict__ base = out + (f_start - ph);   // 16-byte aligned
-    const int F = P * 2 * DD;
+    const int ph = (int)(f_start & (kE - 1));    // phantom elements in front (owned by the previous env); even
+    OutT* __restrict__ base = out + (f_start - ph);    // 16-byte aligned
+    const int F = P * 2 * DD;                    // >= 18 > kE, so head and tail chunks are never the same chunk
     const int L = F + ph;
     const int nW = (L + 31) >> 5;
-    const int nT = (L + kTileFloats - 1) / kTileFloats;
-    const int L4 = L & ~3;                       // floats covered by whole float4s
+    const int nT = (L + kTileElems - 1) / kTileElems;
+    const int L16 = L & ~(kE - 1);               // elements covered by whole 16-byte chunks
 
     auto assemble = [&](const int W) -> uint32_t {
       uint32_t word = 0;
@@ -311,30 +338,37 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       uint32_t word[kWordsPerLane];
 #pragma unroll
       for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
-      float* st = stage + (ring % kStageBufs) * kTileFloats;
+      OutT* st = stage + (ring % kStageBufs) * kTileElems;
       if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
         __syncwarp();
       }
-      float4* st4 = reinterpret_cast<float4*>(st);
+      uint4* st4 = reinterpret_cast<uint4*>(st);
+      constexpr int kSub = 32 / kE;              // 16-byte chunks per stream word (= lanes sharing a word)
 #pragma unroll
       for (int u = 0; u < kWordsPerLane; ++u) {
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {
-          const uint32_t wv = __shfl_sync(kFull, word[u], s * 4 + (lane >> 3));
-          st4[u * 256 + s * 32 + lane] = expand_nibble(wv >> ((lane & 7) * 4));
+        for (int s = 0; s < kSub; ++s) {         // 32 lanes x 16 bytes = 512 contiguous bytes per STS.128
+          const uint32_t wv = __shfl_sync(kFull, word[u], s * kE + lane / kSub);
+          st4[(u * kSub + s) * 32 + lane] = expand_chunk<OutT>(wv >> ((lane & (kSub - 1)) * kE), one16);
         }
       }
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
+      const int f0 = t * kTileElems;
+      // partial 16-byte chunks (shared with the neighbouring envs) go out as element pairs: head on lanes
+      // 0..kE/2-1, tail on lanes 8..8+kE/2-1
+      using PairT = typename OC::PairT;
+      if (t == 0 && ph && lane < kE / 2 && 2 * lane >= ph)
+        __stcs(reinterpret_cast<PairT*>(base) + lane, reinterpret_cast<const PairT*>(st)[lane]);
+      if (t == nT - 1 && lane >= 8 && 2 * (lane - 8) < L - L16)
+        __stcs(reinterpret_cast<PairT*>(base + L16) + (lane - 8),
+               reinterpret_cast<const PairT*>(st + (L16 - f0))[lane - 8]);
       if (lane == 0) {
-        const int f0 = t * kTileFloats;
-        const int lo = (t == 0 && ph) ? 4 : 0;
-        int hi = L4 - f0;
-        if (hi > kTileFloats) hi = kTileFloats;
-        if (t == 0 && ph) st_f2(base + 2, st[2], st[3]);                   // head: floats 2,3 of the first float4
-        if ((L & 3) && t == nT - 1) st_f2(base + L - 2, st[L - 2 - f0], st[L - 1 - f0]);   // tail half float4
-        if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * 4);
+        const int lo = (t == 0 && ph) ? kE : 0;
+        int hi = L16 - f0;
+        if (hi > kTileElems) hi = kTileElems;
+        if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * OC::kB);
         else asm volatile("cp.async.bulk.commit_group;" ::: "memory");     // keep one group per tile
       }
     }

@@ -405,9 +405,9 @@ inline Workspace carve(void* ws, int d, int64_t n) {
 }
 
 // persistent grid: one CTA slot per (SM x resident CTAs), capped by the number of envs
-template <int D>
-void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
-                  int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
+template <int D, typename OutT>
+void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* pos, int64_t* offsets,
+                  int32_t* overflow, int64_t cap, int64_t n, uint32_t one16, cudaStream_t st) {
   using Cfg = PerspCfg<D>;
   constexpr int WPB = Cfg::kWarps;
   static int slots[64] = {0};                     // per device: SMs x resident CTAs of this instantiation
@@ -415,10 +415,11 @@ void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* 
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
   if (slots[dev] == 0) {
-    cudaFuncSetAttribute(persp_write_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    cudaFuncSetAttribute(persp_write_kernel<D, OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         Cfg::kSmemBytes);
     int sms = 148, occ = 1;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persp_write_kernel<D>, WPB * 32, Cfg::kSmemBytes);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persp_write_kernel<D, OutT>, WPB * 32, Cfg::kSmemBytes);
     slots[dev] = sms * (occ > 0 ? occ : 1);
   }
   // TC_WRITE_WAVES: CTAs per resident slot.  0 = one env per warp (the hardware CTA scheduler staggers the
@@ -428,14 +429,15 @@ void launch_write(const uint32_t* syn, const Workspace& w, float* out, uint8_t* 
 #endif
   unsigned grid = grid_for(n, WPB);
   if (TC_WRITE_WAVES > 0 && grid > (unsigned)slots[dev] * TC_WRITE_WAVES) grid = (unsigned)slots[dev] * TC_WRITE_WAVES;
-  persp_write_kernel<D><<<grid, WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb, out, pos,
-                                                                offsets, overflow, cap, n);
+  persp_write_kernel<D, OutT><<<grid, WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb, out,
+                                                                      pos, offsets, overflow, cap, n, one16);
 }
 
-int write_dispatch(int d, const uint32_t* syn, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
-                   int32_t* overflow, int64_t cap, int64_t n, cudaStream_t st) {
+template <typename OutT>
+int write_dispatch(int d, const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* pos, int64_t* offsets,
+                   int32_t* overflow, int64_t cap, int64_t n, uint32_t one16, cudaStream_t st) {
   switch (d) {
-#define TC_CASE(D) case D: launch_write<D>(syn, w, out, pos, offsets, overflow, cap, n, st); break;
+#define TC_CASE(D) case D: launch_write<D, OutT>(syn, w, out, pos, offsets, overflow, cap, n, one16, st); break;
     TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8) TC_CASE(9) TC_CASE(10)
     TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16) TC_CASE(17) TC_CASE(18)
     TC_CASE(19) TC_CASE(20) TC_CASE(21) TC_CASE(22) TC_CASE(23) TC_CASE(24) TC_CASE(25) TC_CASE(26)
@@ -540,15 +542,42 @@ int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void*
   return launch_status();
 }
 
-int tc_persp_write(const uint32_t* syn, float* out, uint8_t* pos, int64_t* offsets, int32_t* overflow,
-                   int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n, void* stream) {
+int tc_persp_write_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* pos, int64_t* offsets,
+                      int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
+                      void* stream) {
   if (bad_d(d) || n < 0 || cap < 0 || !syn || !offsets || !workspace) return -1;
+  if (out_dtype < TC_DTYPE_F32 || out_dtype > TC_DTYPE_F16) return -1;
   if (cap > 0 && !out) return -1;
   if (((uintptr_t)out & 15) || ((uintptr_t)pos & 3)) return -1;
   const Workspace w = carve(workspace, d, n);
   if (workspace_bytes < w.bytes) return -2;
   if (n == 0) return 0;
-  return write_dispatch(d, syn, w, out, pos, offsets, overflow, cap, n, (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (out_dtype) {
+    case TC_DTYPE_F32: return write_dispatch<float>(d, syn, w, (float*)out, pos, offsets, overflow, cap, n, 0u, st);
+    case TC_DTYPE_U8:
+      return write_dispatch<uint8_t>(d, syn, w, (uint8_t*)out, pos, offsets, overflow, cap, n, 0u, st);
+    case TC_DTYPE_BF16:
+      return write_dispatch<uint16_t>(d, syn, w, (uint16_t*)out, pos, offsets, overflow, cap, n, 0x3f80u, st);
+    default:
+      return write_dispatch<uint16_t>(d, syn, w, (uint16_t*)out, pos, offsets, overflow, cap, n, 0x3c00u, st);
+  }
+}
+
+int tc_persp_write(const uint32_t* syn, float* out, uint8_t* pos, int64_t* offsets, int32_t* overflow,
+                   int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n, void* stream) {
+  return tc_persp_write_as(syn, out, TC_DTYPE_F32, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n,
+                           stream);
+}
+
+int tc_perspectives_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* pos, int32_t* counts,
+                       int64_t* offsets, int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes,
+                       int d, int64_t n, void* stream) {
+  if (out_dtype < TC_DTYPE_F32 || out_dtype > TC_DTYPE_F16) return -1;
+  const int rc = tc_persp_count(syn, counts, offsets, workspace, workspace_bytes, d, n, stream);
+  if (rc != 0) return rc;
+  return tc_persp_write_as(syn, out, out_dtype, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n,
+                           stream);
 }
 
 int tc_perspectives(const uint32_t* syn, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,

@@ -22,6 +22,9 @@ ACTOR_FREEZE_DONE = 4
 STATUS_BAD_ACTION = 1
 STATUS_RESET_GAVE_UP = 2
 
+# element types of the perspective tensor (include/toric_b200.h TC_DTYPE_*)
+OUT_DTYPES = {torch.float32: 0, torch.uint8: 1, torch.bfloat16: 2, torch.float16: 3}
+
 COUNTER_NAMES = ("env_steps", "episodes", "solved", "ground_kept", "timeouts", "perspectives",
                  "err_x", "err_y", "err_z", "qubits_sampled", "reset_attempts", "bad_actions")
 
@@ -47,8 +50,14 @@ class ToricEngine:
     syn int32[n,2,d] (vertex, plaquette planes).
     """
 
-    def __init__(self, d, n, device="cuda", seed=0, env_base=0, p_error=0.1, max_steps=75):
+    def __init__(self, d, n, device="cuda", seed=0, env_base=0, p_error=0.1, max_steps=75,
+                 out_dtype=torch.float32):
+        """out_dtype: element type of the perspective tensor -- float32 (the reference's,
+        src/numba/util_actor.py:39), or bfloat16 / float16 / uint8 (same 0/1 values, 2-4x less HBM traffic)."""
         self.lib = _lib.load()
+        if out_dtype not in OUT_DTYPES:
+            raise ValueError("out_dtype must be one of %s" % (sorted(str(k) for k in OUT_DTYPES),))
+        self.out_dtype = out_dtype
         if not (3 <= int(d) <= 32):
             raise ValueError("lattice size d must be in [3, 32]")
         if not torch.cuda.is_available():
@@ -76,7 +85,7 @@ class ToricEngine:
         nbytes = ctypes.c_size_t(0)
         _lib.check(self.lib.tc_workspace_bytes(d_, n_, ctypes.byref(nbytes)), "tc_workspace_bytes")
         self.workspace = z(max(int(nbytes.value), 256), torch.uint8)
-        self.out = None       # float32 [cap, 2, d, d]
+        self.out = None       # out_dtype [cap, 2, d, d]
         self.pos = None       # uint8   [cap, 4]
         self.cap = 0
         self.set_p_error(p_error)
@@ -100,7 +109,7 @@ class ToricEngine:
         if cap > self.cap:
             self.out = None
             self.pos = None
-            self.out = torch.empty((cap, 2, self.d, self.d), dtype=torch.float32, device=self.device)
+            self.out = torch.empty((cap, 2, self.d, self.d), dtype=self.out_dtype, device=self.device)
             self.pos = torch.empty((cap, 4), dtype=torch.uint8, device=self.device)
             self.cap = cap
 
@@ -179,9 +188,10 @@ class ToricEngine:
         if self.out is None:
             self.ensure_capacity(self.worst_case_capacity())
         self.overflow.zero_()
-        _lib.check(self.lib.tc_perspectives(_ptr(syn), _ptr(self.out), _ptr(self.pos), _ptr(self.counts),
-                                            _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace),
-                                            self.workspace.numel(), self.d, n, _stream()), "tc_perspectives")
+        _lib.check(self.lib.tc_perspectives_as(_ptr(syn), _ptr(self.out), OUT_DTYPES[self.out_dtype], _ptr(self.pos),
+                                               _ptr(self.counts), _ptr(self.offsets), _ptr(self.overflow), self.cap,
+                                               _ptr(self.workspace), self.workspace.numel(), self.d, n, _stream()),
+                   "tc_perspectives_as")
 
     def perspectives_count(self, syn=None, n=None):
         """Count + scan only (tc_persp_count): fills counts and offsets[n] = total, writes no perspectives."""
@@ -210,6 +220,15 @@ class ToricEngine:
             self.ensure_capacity(self.worst_case_capacity())
         self._last_syn = self.syn
         self.overflow.zero_()
+        if self.out_dtype is not torch.float32:      # fused entry point is float32; same two halves otherwise
+            _lib.check(self.lib.tc_actor_pre(
+                _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
+                _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+                _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
+                int(n_fixed), self.seed, self.env_base, _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace),
+                self.workspace.numel(), self.d, self.n, _stream()), "tc_actor_pre")
+            self.persp_write()
+            return
         _lib.check(self.lib.tc_actor_step(
             _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
             _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
@@ -238,9 +257,10 @@ class ToricEngine:
         """Second half: the streaming perspective write for the state left by actor_pre()."""
         if self.out is None:
             self.ensure_capacity(self.worst_case_capacity())
-        _lib.check(self.lib.tc_persp_write(_ptr(self.syn), _ptr(self.out), _ptr(self.pos), _ptr(self.offsets),
-                                           _ptr(self.overflow), self.cap, _ptr(self.workspace),
-                                           self.workspace.numel(), self.d, self.n, _stream()), "tc_persp_write")
+        _lib.check(self.lib.tc_persp_write_as(_ptr(self.syn), _ptr(self.out), OUT_DTYPES[self.out_dtype],
+                                              _ptr(self.pos), _ptr(self.offsets), _ptr(self.overflow), self.cap,
+                                              _ptr(self.workspace), self.workspace.numel(), self.d, self.n,
+                                              _stream()), "tc_persp_write_as")
 
     # -- results ---------------------------------------------------------------------------------
     def total_perspectives(self, n=None):
@@ -249,7 +269,7 @@ class ToricEngine:
         return int(self.offsets[n].item())
 
     def perspective_views(self, n=None):
-        """(persp float32 (sumP,2,d,d), pos uint8 (sumP,4), counts int32 (n,), offsets int64 (n+1,)) as
+        """(persp out_dtype (sumP,2,d,d), pos uint8 (sumP,4), counts int32 (n,), offsets int64 (n+1,)) as
         views of the engine buffers.  Synchronises to learn sumP; regenerates if the buffer overflowed."""
         n = self.n if n is None else n
         total = self.total_perspectives(n)
