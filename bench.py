@@ -264,9 +264,10 @@ def run_b200(a):
             pass
 
     # ---- e2e: reference-facing call with HOST buffers (actions in, step results out) ----------
-    e2e = None
+    e2e = e2e_rows = None
     if not a.no_e2e:
-        e2e = run_e2e(a, eng, dev, dist, barrier, world)
+        e2e = run_e2e(a, eng, dev, dist, barrier, world, "u8")
+        e2e_rows = run_e2e(a, eng, dev, dist, barrier, world, "rows")
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -285,7 +286,8 @@ def run_b200(a):
                            "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
                                  % (wbytes / 1e9),
                            "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": 3 * a.steps,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_state_rows": e2e_rows,
+                "gpu_launches": 3 * a.steps,
                 "clocks": clk.summary(),
                 "counters": {k: c[k] for k in ("episodes", "solved", "ground_kept", "timeouts", "perspectives")}}
         print(json.dumps(line), flush=True)
@@ -293,14 +295,17 @@ def run_b200(a):
         dist.destroy_process_group()
 
 
-def run_e2e(a, eng, dev, dist, barrier, world):
+def run_e2e(a, eng, dev, dist, barrier, world, states):
     """Same metric through the host-facing call (toric_rl_decoder_b200.HostActorPipeline): every step copies
     that step's actions (n,4) int32 from pinned host memory, runs the fused actor step, and reads rewards,
     terminals, perspective counts and the new states (uint8 n,2,d,d) back to pinned host memory.  Uploads
     and downloads run on their own streams with up to three steps in flight; every step's results are read on
     the host inside the timed region.
     The perspective tensor stays on the device, where the reference also puts it (`.to(device)`,
-    src/numba/util_actor.py:39)."""
+    src/numba/util_actor.py:39).  states="u8" (the `e2e` key) downloads the reference's one-byte-per-stabiliser
+    array; states="rows" (`e2e_state_rows`) downloads np.packbits(states, axis=-1, bitorder="little") instead --
+    at 8 ranks the box's aggregate device->host rate (~90 GB/s, profiles/r01_e2e_scale_probe.txt), not the
+    GPUs, bounds the u8 form."""
     import numpy as np
     import torch
     from toric_rl_decoder_b200 import HostActorPipeline, sharding
@@ -313,7 +318,8 @@ def run_e2e(a, eng, dev, dist, barrier, world):
                        axis=1).astype(np.int32)
         host_actions.append(torch.from_numpy(arr).pin_memory())
     depth = 3
-    pipe = HostActorPipeline(eng, depth=depth)
+    pipe = HostActorPipeline(eng, depth=depth, states=states)
+    skey = "states" if states == "u8" else "state_rows"
     checksum = 0.0
 
     def run(steps):
@@ -321,7 +327,7 @@ def run_e2e(a, eng, dev, dist, barrier, world):
         for k in range(steps):
             if pipe.submitted - pipe.collected >= depth:
                 res = pipe.collect()                    # the oldest step in flight is in host memory now
-                checksum += float(res["reward"][0]) + float(res["states"][0, 0, 0, 0])
+                checksum += float(res["reward"][0]) + float(res[skey][0, 0, 0, 0])
             pipe.submit(host_actions[k % n_buf], auto_reset=True)
         while pipe.collected < pipe.submitted:
             res = pipe.collect()
@@ -342,7 +348,9 @@ def run_e2e(a, eng, dev, dist, barrier, world):
             "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
             "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
             "call": "HostActorPipeline.submit(pinned host actions) / collect() -> host reward, terminal, counts, "
-                    "states; uploads and downloads on their own streams, up to 3 steps in flight",
+                    "%s; uploads and downloads on their own streams, up to 3 steps in flight"
+                    % ("states uint8 (n,2,d,d)" if states == "u8" else
+                       "state_rows uint8 (n,2,d,ceil(d/8)) = packbits(states, little)"),
             "policy": "host-supplied uniformly random qubit + Pauli"}
 
 

@@ -63,6 +63,10 @@ int tc_unpack_qubits(const uint32_t* qubits, uint8_t* codes, int d, int64_t n, v
 /* state01: uint8 [n][2][d][d] of 0/1 (any non-zero counts as a defect when packing). */
 int tc_pack_state(const uint8_t* state01, uint32_t* syn, int d, int64_t n, void* stream);
 int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, void* stream);
+/* The same state as lattice-row bitmasks: rows uint8 [n][2][d][ceil(d/8)] = numpy
+ * packbits(state, axis=-1, bitorder="little") -- the compact host format of the new states (a step result of
+ * EnvSet.step, src/EnvSet.py:38-47) for callers that read every step's states back over PCIe. */
+int tc_state_rows(const uint32_t* syn, uint8_t* rows, int d, int64_t n, void* stream);
 
 /* createSyndromOpt (ToricCode.py:168-199): syn <- stencil(qubits). */
 int tc_syndrome(const uint32_t* qubits, uint32_t* syn, int d, int64_t n, void* stream);

@@ -216,9 +216,10 @@ def test_full_size_properties(pkg, d, n):
     assert torch.equal(before, eng.syn)
 
 
-def test_host_pipeline_matches_oracle(pkg):
+@pytest.mark.parametrize("d,states", ((7, "u8"), (7, "rows"), (13, "rows"), (5, None)))
+def test_host_pipeline_matches_oracle(pkg, d, states):
     """HostActorPipeline (pinned host actions in, host results out, two steps in flight) == the numpy oracle."""
-    d, n, steps = 7, 300, 12
+    n, steps = 300, 12
     eng = pkg.ToricEngine(d, n, seed=5, p_error=0.1, max_steps=1000)
     eng.reset()
     q = eng.get_qubits().cpu().numpy().astype(np.int64)
@@ -227,7 +228,7 @@ def test_host_pipeline_matches_oracle(pkg):
     acts = [np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)],
                      axis=1).astype(np.int32) for _ in range(steps)]
     pinned = [torch.from_numpy(a).pin_memory() for a in acts]
-    pipe = pkg.HostActorPipeline(eng, depth=2)
+    pipe = pkg.HostActorPipeline(eng, depth=2, states=states)
     got = []
     for k in range(steps):
         pipe.submit(pinned[k], auto_reset=False)
@@ -240,6 +241,12 @@ def test_host_pipeline_matches_oracle(pkg):
         for e in range(n):
             q[e], s[e], rew, term = O.step(q[e], s[e], acts[k][e])
             assert got[k]["reward"][e] == rew and bool(got[k]["terminal"][e]) == term
-        assert (got[k]["states"] == s).all()
+        if states == "u8":
+            assert (got[k]["states"] == s).all()
+        elif states == "rows":
+            assert (got[k]["state_rows"] == np.packbits(s.astype(np.uint8), axis=-1, bitorder="little")).all()
+            assert (pipe.unpack_rows(got[k]["state_rows"]) == s).all()
+        else:
+            assert "states" not in got[k] and "state_rows" not in got[k]
         _, _, counts, _ = O.perspectives_batch(s)
         assert (got[k]["counts"] == counts).all()

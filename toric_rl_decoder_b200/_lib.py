@@ -19,6 +19,7 @@ SIGNATURES = {
     "tc_unpack_qubits": [_vp, _vp, _i, _i64, _vp],
     "tc_pack_state": [_vp, _vp, _i, _i64, _vp],
     "tc_unpack_state": [_vp, _vp, _i, _i64, _vp],
+    "tc_state_rows": [_vp, _vp, _i, _i64, _vp],
     "tc_syndrome": [_vp, _vp, _i, _i64, _vp],
     "tc_step": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _vp],
     "tc_reset": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _u64, _i64, _i, _vp],

@@ -64,6 +64,16 @@ __global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* _
   for (int j = 0; j < d; ++j) dst[j] = (uint8_t)((w >> j) & 1u);
 }
 
+// row words -> np.packbits(state, axis=-1, bitorder="little"): ceil(d/8) bytes per lattice row
+__global__ void state_rows_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ rows, int d, int nb,
+                                  int64_t n) {
+  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * 2 * d * nb) return;
+  const int64_t r = t / nb;
+  const int b = (int)(t - r * nb);
+  rows[t] = (uint8_t)(syn[r] >> (8 * b));
+}
+
 // ------------------------------------------------------------------------------------------------
 // K2 syndrome, K3 step, K1 reset, K5 ground state (standalone forms)
 // ------------------------------------------------------------------------------------------------
@@ -485,6 +495,14 @@ int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, voi
   if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
   if (n == 0) return 0;
   unpack_state_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, n);
+  return launch_status();
+}
+
+int tc_state_rows(const uint32_t* syn, uint8_t* rows, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0 || !rows || !syn) return -1;
+  if (n == 0) return 0;
+  const int nb = (d + 7) / 8;
+  state_rows_kernel<<<grid_for(n * 2 * d * nb, 256), 256, 0, (cudaStream_t)stream>>>(syn, rows, d, nb, n);
   return launch_status();
 }
 

@@ -24,9 +24,18 @@ from .engine import _ptr
 
 
 class HostActorPipeline:
-    def __init__(self, engine, depth=2):
+    def __init__(self, engine, depth=2, states="u8"):
+        """states: how each step's new states reach the host (rewards, terminals and perspective counts
+        always do):
+          "u8"   uint8 (n,2,d,d) of 0/1 -- the reference's array (src/EnvSet.py:39,47), one byte per stabiliser;
+          "rows" uint8 (n,2,d,ceil(d/8)) = np.packbits(states, axis=-1, bitorder="little") -- 7x fewer PCIe
+                 bytes at d=7 (`unpack_rows` restores the (n,2,d,d) array);
+          None   states stay on the device."""
+        if states not in ("u8", "rows", None):
+            raise ValueError('states must be "u8", "rows" or None')
         self.eng = engine
         self.depth = int(depth)
+        self.states = states
         n, d = engine.n, engine.d
         dev = engine.device
         self.h2d_stream = torch.cuda.Stream(device=dev)
@@ -35,7 +44,9 @@ class HostActorPipeline:
         self.o_counts = 4 * n
         self.o_term = 8 * n
         self.o_state = (9 * n + 15) & ~15
-        self.nbytes = self.o_state + n * 2 * d * d
+        self.row_bytes = (d + 7) // 8
+        self.state_bytes = {"u8": n * 2 * d * d, "rows": n * 2 * d * self.row_bytes, None: 0}[states]
+        self.nbytes = self.o_state + self.state_bytes
         self.h2d_bytes = n * 16
         self.d2h_bytes = self.nbytes
         self.slots = []
@@ -52,13 +63,17 @@ class HostActorPipeline:
                 "reward": hs[self.o_reward:self.o_reward + 4 * n].view(np.float32),
                 "counts": hs[self.o_counts:self.o_counts + 4 * n].view(np.int32),
                 "terminal": hs[self.o_term:self.o_term + n].view(np.bool_),
-                "states": hs[self.o_state:self.o_state + n * 2 * d * d].reshape(n, 2, d, d),
             }
+            if states == "u8":
+                slot["views"]["states"] = hs[self.o_state:self.o_state + self.state_bytes].reshape(n, 2, d, d)
+            elif states == "rows":
+                slot["views"]["state_rows"] = hs[self.o_state:self.o_state + self.state_bytes].reshape(
+                    n, 2, d, self.row_bytes)
             ds = slot["d_stage"]
             slot["d_reward"] = ds[self.o_reward:self.o_reward + 4 * n].view(torch.float32)
             slot["d_counts"] = ds[self.o_counts:self.o_counts + 4 * n].view(torch.int32)
             slot["d_term"] = ds[self.o_term:self.o_term + n]
-            slot["d_state"] = ds[self.o_state:self.o_state + n * 2 * d * d]
+            slot["d_state"] = ds[self.o_state:self.o_state + self.state_bytes]
             self.slots.append(slot)
         self.submitted = 0
         self.collected = 0
@@ -79,8 +94,12 @@ class HostActorPipeline:
         slot["d_reward"].copy_(eng.reward, non_blocking=True)
         slot["d_counts"].copy_(eng.counts, non_blocking=True)
         slot["d_term"].copy_(eng.terminal, non_blocking=True)
-        _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
-                                           compute.cuda_stream), "tc_unpack_state")
+        if self.states == "u8":
+            _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
+                                               compute.cuda_stream), "tc_unpack_state")
+        elif self.states == "rows":
+            _lib.check(eng.lib.tc_state_rows(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
+                                             compute.cuda_stream), "tc_state_rows")
         slot["ev_compute"].record(compute)
         with torch.cuda.stream(self.d2h_stream):
             self.d2h_stream.wait_event(slot["ev_compute"])
@@ -90,14 +109,18 @@ class HostActorPipeline:
 
     def collect(self):
         """Block until the oldest outstanding step's results are in host memory; returns numpy views
-        {reward f32 (n,), counts i32 (n,), terminal bool (n,), states u8 (n,2,d,d)} valid until the slot is
-        reused (depth submits later)."""
+        {reward f32 (n,), counts i32 (n,), terminal bool (n,), states u8 (n,2,d,d) | state_rows u8
+        (n,2,d,ceil(d/8))} valid until the slot is reused (depth submits later)."""
         if self.collected >= self.submitted:
             raise RuntimeError("nothing to collect")
         slot = self.slots[self.collected % self.depth]
         slot["ev_result"].synchronize()
         self.collected += 1
         return slot["views"]
+
+    def unpack_rows(self, state_rows):
+        """(n,2,d,ceil(d/8)) row bitmasks -> the reference's (n,2,d,d) 0/1 array (host, numpy)."""
+        return np.unpackbits(state_rows, axis=-1, bitorder="little")[..., :self.eng.d]
 
     def step(self, actions_host, auto_reset=True):
         """Unpipelined convenience form: submit + collect."""

@@ -42,6 +42,35 @@ def init_from_env(backend=None):
     return rank, world, local
 
 
+def bind_to_gpu_numa(local_gpu):
+    """Pin the calling process to the CPU cores NVML reports as closest to GPU `local_gpu` (same NUMA node /
+    PCIe root), so that the pinned host buffers it allocates afterwards are NUMA-local to that GPU.  Matters
+    when 8 ranks stream results to host memory at once; a no-op when NVML or the affinity call is unavailable.
+    Returns the number of CPUs in the mask (0 if nothing was changed)."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        idx = int(local_gpu)
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                idx = int(vis.split(",")[idx])
+            except Exception:
+                pass
+        h = nv.nvmlDeviceGetHandleByIndex(idx)
+        ncpu = os.cpu_count() or 1
+        words = nv.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, m in enumerate(words) for b in range(64) if (int(m) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus or cpus == allowed:
+            return 0
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return 0
+
+
 def allreduce_counters(counters, group=None):
     """Sum the engine's int64 counter vector over all ranks (in place) and return it."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
