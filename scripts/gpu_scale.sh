@@ -16,8 +16,9 @@ for n in 1 2 4 8; do
 import json, sys
 try:
     j = json.loads([l for l in open(sys.argv[1]) if l.startswith("{")][-1])
-    print("N=%d value %.4e env-steps/s  step %.4f ms  e2e %.4e  writer frac %.3f" % (
-        j["n_gpus"], j["value"], j["ms_per_step"], j["e2e"]["value"], j["roofline"]["frac"]))
+    print("N=%d value %.4e env-steps/s  step %.4f ms  e2e %.4e  e2e(state rows) %.4e  writer frac %.3f" % (
+        j["n_gpus"], j["value"], j["ms_per_step"], j["e2e"]["value"], j["e2e_state_rows"]["value"],
+        j["roofline"]["frac"]))
 except Exception as e:
     print("parse failed", e)
 PY
