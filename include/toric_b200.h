@@ -39,6 +39,9 @@ extern "C" {
 #define TC_SAMPLE_DEPOLARIZING 0 /* generateRandomError, ToricCode.py:130-151 */
 #define TC_SAMPLE_FIXED_WEIGHT 1 /* generateNRandomErrors, ToricCode.py:153-166 */
 #define TC_SAMPLE_FIXED_PLUS_P 2 /* generateNPlusQRandomErrors, results/small_p_error_test.py:43-52 */
+/* tc_reset only, OR-ed into the mode: one draw of the generator without reset()'s rejection of trivial
+ * syndromes -- the generators called on their own (ToricCode.py:130-166) */
+#define TC_SAMPLE_ONE_DRAW 16
 
 /* flags of tc_actor_step */
 #define TC_ACTOR_RANDOM_ACTIONS 1 /* draw the action on device (uniform over the perspective list x {X,Y,Z}) */

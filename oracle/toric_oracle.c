@@ -130,6 +130,8 @@ static inline uint32_t mulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint6
 uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episode, uint32_t thresh, int mode,
                   int n_fixed, uint64_t seed) {
   const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+  const int one_draw = mode & 16;     /* bare generator call: no rejection of trivial syndromes */
+  mode &= 3;
   const int nq = 2 * d * d;
   const int nf = n_fixed < nq ? n_fixed : nq;
   uint32_t pm = 1;
@@ -167,7 +169,7 @@ uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episo
     }
     to_syndrome(q, s, d);
     ++attempt;
-    if (defects(s, d) != 0) return attempt;
+    if (defects(s, d) != 0 || one_draw) return attempt;
     if (attempt >= cap) return 0x80000000u | attempt;
   }
 }

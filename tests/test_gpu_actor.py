@@ -47,6 +47,40 @@ def test_reset_matches_sampler_spec(pkg, d, mode, n_fixed, p):
             assert (q2[e] == q[e]).all()
 
 
+def test_bare_generators(pkg):
+    """generateRandomError / generateNRandomErrors called on their own (ToricCode.py:130-166): one draw of the
+    device sampler without reset()'s rejection -- bit-exact vs the C oracle's one-draw mode, statistics of
+    the reference's distribution (trivial syndromes included), env state untouched."""
+    d, seed = 5, 77
+    env = pkg.ToricCodeB200({"size": d, "p_error": 0.1}, seed=seed, env_base=9)
+    s0 = env.reset()
+    p = 0.004                                     # most draws have no error at all: never rejected
+    th = int(pkg.p_to_thresh(p))
+    n_empty = 0
+    for k in range(40):
+        m = env.generateRandomError(np.zeros((2, d, d), dtype=int), p)
+        cq, _, att = C.reset(d, 9 + (1 << 40), k, th, seed, mode=16)
+        assert att == 1 and m.shape == (2, d, d) and (m == cq).all()
+        n_empty += int(not m.any())
+    assert n_empty > 20
+    buf = np.zeros((2, d, d), dtype=int)
+    for k in range(10):
+        out = env.generateNRandomErrors(buf, 3)
+        cq, _, att = C.reset(d, 9 + (1 << 40), 40 + k, th, seed, mode=1 | 16, n_fixed=3)
+        assert out is buf and (buf == cq).all() and (buf != 0).sum() == 3
+    assert (env.generateNRandomErrors(buf, 0) == 0).all()
+    assert (env.state == s0).all()
+    # raw ABI: one-draw over a batch at p=0.1 reproduces the unconditional per-qubit rate
+    n = 20000
+    eng = pkg.ToricEngine(7, n, seed=1, p_error=0.1)
+    eng.reset(mode=16)
+    q = eng.get_qubits().cpu().numpy()
+    rate = (q != 0).mean()
+    assert abs(rate - 0.1) < 5 * np.sqrt(0.1 * 0.9 / q.size)
+    for c in (1, 2, 3):
+        assert abs((q == c).mean() - 0.1 / 3) < 5 * np.sqrt(0.0333 * 0.9667 / q.size)
+
+
 @pytest.mark.parametrize("d,n,steps,max_steps,p", ((7, 512, 100, 75, 0.1), (5, 384, 60, 4, 0.02), (9, 128, 30, 10, 0.1),
                                                     (4, 64, 40, 6, 0.1), (17, 48, 12, 5, 0.05)))
 def test_fused_actor_trajectory_bit_exact(pkg, d, n, steps, max_steps, p):

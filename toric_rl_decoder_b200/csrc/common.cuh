@@ -70,6 +70,7 @@ constexpr uint32_t kDomFixed = 0x80000000u;    // fixed-weight sampler draws
 constexpr uint32_t kDomAction = 0xC0000000u;   // random-policy action draws
 constexpr uint32_t kMaxAttempts = 1u << 20;    // depolarizing rejection attempts
 constexpr uint32_t kMaxFixedAttempts = 1u << 10;
+constexpr int kSampleOneDraw = 16;             // TC_SAMPLE_ONE_DRAW (OR-ed into the sampling mode)
 
 // ---------------------------------------------------------------------------------------------
 // d-bit row helpers

@@ -104,6 +104,8 @@ template <int G>
 __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint64_t env_id, uint32_t episode,
                                               uint32_t thresh, int mode, int n_fixed, uint2 key, Rows& s,
                                               uint8_t& status, SampleStats& st) {
+  const bool one_draw = (mode & kSampleOneDraw) != 0;   // the bare generators: no non-trivial-syndrome rejection
+  mode &= 3;
   const int nq = 2 * d * d;
   const int nf = n_fixed < nq ? n_fixed : nq;
   uint32_t pm = 1;
@@ -168,7 +170,7 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
     syndrome_rows<G>(gmask, d, r, s);
     const uint32_t any = __ballot_sync(gmask, (s.v | s.pl) != 0u) & gmask;
     ++attempt;
-    if (any) break;
+    if (any || one_draw) break;
     if (attempt >= cap) { status |= kStatusResetGaveUp; break; }
   }
   st.attempts = (int)attempt;

@@ -528,7 +528,8 @@ int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, cons
              uint32_t* episode, const int64_t* idx, int64_t n_idx, int mode, int n_fixed, uint64_t seed,
              int64_t env_base, int d, void* stream) {
   if (bad_d(d) || n_idx < 0 || !qubits || !syn || !p_thresh || !episode) return -1;
-  if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
+  const int base_mode = mode & ~TC_SAMPLE_ONE_DRAW;
+  if (base_mode < 0 || base_mode > 2 || n_fixed < 0 || (base_mode != 0 && n_fixed == 0)) return -1;
   if (n_idx == 0) return 0;
   TC_DISPATCH_G(d, (reset_kernel<G><<<grid_for(n_idx * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                        qubits, syn, gs, status, p_thresh, episode, idx, n_idx, mode, n_fixed, make_key(seed),

@@ -14,6 +14,7 @@ from . import _lib
 SAMPLE_DEPOLARIZING = 0   # generateRandomError        (ToricCode.py:130-151)
 SAMPLE_FIXED_WEIGHT = 1   # generateNRandomErrors      (ToricCode.py:153-166)
 SAMPLE_FIXED_PLUS_P = 2   # generateNPlusQRandomErrors (results/small_p_error_test.py:43-52)
+SAMPLE_ONE_DRAW = 16      # OR-ed into the mode: one generator draw, no rejection of trivial syndromes
 
 ACTOR_RANDOM_ACTIONS = 1
 ACTOR_AUTO_RESET = 2

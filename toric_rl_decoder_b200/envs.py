@@ -11,7 +11,7 @@ from collections import namedtuple
 import numpy as np
 import torch
 
-from .engine import (SAMPLE_DEPOLARIZING, SAMPLE_FIXED_WEIGHT, ToricEngine)
+from .engine import (SAMPLE_DEPOLARIZING, SAMPLE_FIXED_WEIGHT, SAMPLE_ONE_DRAW, ToricEngine)
 
 _Box = namedtuple("Box", ["low", "high", "shape"])
 
@@ -42,6 +42,7 @@ class ToricCodeB200:
         self.observation_space = _Box(0, 1, (2, d, d))
         self.rule_table = np.array([[0, 1, 2, 3], [1, 0, 3, 2], [2, 3, 0, 1], [3, 2, 1, 0]], dtype=int)
         self._eng = ToricEngine(d, 1, device=device, seed=seed, env_base=env_base, p_error=self.p_error)
+        self._scratch = None      # second engine for the pure functions (createSyndromOpt, generate*Error*)
         self.next_state = self.state
 
     # -- attribute surface -------------------------------------------------------------------------
@@ -90,9 +91,17 @@ class ToricCodeB200:
         self.next_state = self.state
         return self.next_state, int(r), bool(terminal[0].item()), {}
 
+    def _scratch_engine(self):
+        if self._scratch is None:
+            e = self._eng
+            # its own Philox stream: same seed, env id far outside any batch
+            self._scratch = ToricEngine(self.system_size, 1, device=e.device, seed=e.seed,
+                                        env_base=e.env_base + (1 << 40))
+        return self._scratch
+
     def createSyndromOpt(self, tcode):
         """createSyndromOpt (ToricCode.py:168-199) of an arbitrary qubit matrix (scratch engine state)."""
-        eng = ToricEngine(self.system_size, 1, device=self._eng.device)
+        eng = self._scratch_engine()
         eng.set_qubits(np.asarray(tcode).astype(np.uint8)[None])
         return eng.get_state()[0].cpu().numpy().astype(np.int64)
 
@@ -104,8 +113,24 @@ class ToricCodeB200:
         return bool(self._eng.ground_state()[0].item())
 
     def generateRandomError(self, matrix, p_error):
-        """generateRandomError (ToricCode.py:130-151) drawn by the device sampler (no rejection)."""
-        raise NotImplementedError("use reset(); the device sampler always applies the non-trivial-syndrome rejection")
+        """generateRandomError (ToricCode.py:130-151): a fresh (2,d,d) matrix with independent errors of
+        probability p_error and uniform Pauli codes 1..3 -- one draw of the device sampler, no rejection;
+        like the reference it ignores the contents of `matrix` and leaves the env untouched."""
+        eng = self._scratch_engine()
+        eng.set_p_error(float(p_error))
+        eng.reset(mode=SAMPLE_DEPOLARIZING | SAMPLE_ONE_DRAW)
+        return eng.get_qubits()[0].cpu().numpy().astype(np.int64)
+
+    def generateNRandomErrors(self, matrix, n):
+        """generateNRandomErrors (ToricCode.py:153-166): exactly n errors on a uniform random n-subset of the
+        2d^2 qubits, uniform codes 1..3; written into `matrix` in place and returned, as the reference does."""
+        eng = self._scratch_engine()
+        if int(n) <= 0:
+            matrix[:, :, :] = 0
+            return matrix
+        eng.reset(mode=SAMPLE_FIXED_WEIGHT | SAMPLE_ONE_DRAW, n_fixed=int(n))
+        matrix[:, :, :] = eng.get_qubits()[0].cpu().numpy()
+        return matrix
 
     def render(self, mode="human"):
         pass
