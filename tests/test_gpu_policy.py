@@ -177,3 +177,32 @@ def test_freeze_done_leaves_solved_envs_untouched(pkg):
     assert steps[1] == 1 and steps[3] == 1 and eng.terminal.cpu().numpy()[1] == 1 and st[1].sum() == 0
     assert st[3].sum() > 0
     assert eng.read_counters()["env_steps"] == 2
+
+
+@pytest.mark.parametrize("d", (3, 4, 5, 7, 8, 9, 16, 25))
+def test_rotate_and_shift_state(pkg, d):
+    """rotate_state / shift_state host mirrors (src/util.py:87-102) == numpy restatement of the reference's
+    np.rot90 / np.roll lines, every (row, col) of the lattice for the shift."""
+    from oracle import toric_oracle as O
+    rng = np.random.default_rng(d)
+    for _ in range(3):
+        st = (rng.random((2, d, d)) < 0.3).astype(np.int64)
+        prev = (rng.random((2, d, d)) < 0.3).astype(np.int64)
+        want = np.stack((np.roll(np.rot90(st[0]), 1, axis=0), np.rot90(st[1])))
+        got = pkg.rotate_state(st)
+        assert got.dtype == np.int64 and (got == want).all() and (got == O.rotate_state(st)).all()
+        g = d // 2
+        for row, col in ((0, 0), (d - 1, d - 1), (g, g), (int(rng.integers(d)), int(rng.integers(d)))):
+            a, b = pkg.shift_state(row, col, prev, st, g)
+            wa = np.roll(np.roll(prev, g - row, axis=1), g - col, axis=2)
+            wb = np.roll(np.roll(st, g - row, axis=1), g - col, axis=2)
+            assert (a == wa).all() and (b == wb).all()
+
+
+def test_make_mirrors_gym_make(pkg):
+    env = pkg.make("toric-code-v0", config={"size": 5, "p_error": 0.1})
+    assert env.system_size == 5 and env.action_space.high[-1] == 3
+    s = env.reset()
+    assert s.shape == (2, 5, 5) and s.any()
+    with pytest.raises(ValueError):
+        pkg.make("cartpole")

@@ -7,9 +7,10 @@ libtoric_b200.so (C ABI: include/toric_b200.h); importing the package does not n
 from .buildlib import LIB_PATH, build  # noqa: F401
 from .engine import (ACTOR_AUTO_RESET, ACTOR_RANDOM_ACTIONS, SAMPLE_DEPOLARIZING, SAMPLE_FIXED_PLUS_P,  # noqa: F401
                      SAMPLE_FIXED_WEIGHT, ToricEngine, p_to_thresh)
-from .envs import EnvSetB200, ToricCodeB200  # noqa: F401
+from .envs import EnvSetB200, ToricCodeB200, make  # noqa: F401
 from .perspectives import (Perspective, generatePerspective, generatePerspectiveBatch,  # noqa: F401
                            generatePerspectiveOptimized)
 from .policy import (computePrioritiesParallel, generateTransitionParallel, predictMaxOptimized,  # noqa: F401
-                     selectAction, selectActionBatch, select_action_device, transitions_device)
+                     rotate_state, selectAction, selectActionBatch, select_action_device, shift_state,
+                     transitions_device)
 from .hostpipe import HostActorPipeline  # noqa: F401

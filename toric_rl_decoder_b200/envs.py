@@ -195,3 +195,27 @@ class EnvSetB200:
             return (st.cpu().numpy().astype(np.int64), reward.cpu().numpy().astype(np.float64),
                     terminal.cpu().numpy().astype(bool), {})
         return st, reward, terminal.bool(), {}
+
+
+ENV_ID = "toric-code-b200-v0"
+
+
+def make(env_id=ENV_ID, config=None, **kwargs):
+    """gym.make('toric-code-v0', config=...) (gym_ToricCode/__init__.py:3-6) without needing gym: both the
+    reference's id and ENV_ID give a ToricCodeB200."""
+    if env_id not in (ENV_ID, "toric-code-v0"):
+        raise ValueError("unknown environment id %r" % (env_id,))
+    return ToricCodeB200(config, **kwargs)
+
+
+def _register_with_gym():
+    """If gym is importable, `gym.make(ENV_ID, config=...)` works like the reference's registration."""
+    try:
+        from gym.envs.registration import register
+        register(id=ENV_ID, entry_point="toric_rl_decoder_b200.envs:ToricCodeB200")
+        return True
+    except Exception:
+        return False
+
+
+_register_with_gym()

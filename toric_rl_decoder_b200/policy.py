@@ -81,8 +81,8 @@ def transitions_device(syn_prev, syn_next, actions, d, out_dtype=torch.float32):
     n = actions.shape[0]
     dev = actions.device
     code = {torch.float32: DTYPE_F32, torch.uint8: DTYPE_U8}[out_dtype]
-    op = torch.empty((n, 2, d, d), dtype=out_dtype, device=dev)
-    on = torch.empty((n, 2, d, d), dtype=out_dtype, device=dev)
+    op = torch.empty((n, 2, d, d), dtype=out_dtype, device=dev) if syn_prev is not None else None
+    on = torch.empty((n, 2, d, d), dtype=out_dtype, device=dev) if syn_next is not None else None
     ao = torch.empty((n, 4), dtype=torch.int32, device=dev)
     _lib.check(lib.tc_transitions(_ptr(syn_prev), _ptr(syn_next), _ptr(actions), _ptr(op), _ptr(on), _ptr(ao),
                                   code, int(d), int(n), _stream()), "tc_transitions")
@@ -96,6 +96,33 @@ def _pack(states, d, dev):
     syn = torch.empty((u8.shape[0], 2, d), dtype=torch.int32, device=dev)
     _lib.check(lib.tc_pack_state(_ptr(u8), _ptr(syn), d, u8.shape[0], _stream()), "tc_pack_state")
     return syn
+
+
+def rotate_state(state, device="cuda"):
+    """rotate_state (src/util.py:87-94; numba twin src/numba/util.py:17-25): counter-clockwise rot90 of both
+    planes, vertex plane then rolled by +1 along axis 0.  (2,d,d) in, int64 (2,d,d) out.  Computed by the
+    transition kernel: acting on qubit (1,g,g) needs no shift, only the matrix-1 rotation."""
+    st = np.asarray(state)
+    d = int(st.shape[-1])
+    dev = torch.device(device)
+    syn = _pack(st[None], d, dev)
+    act = torch.tensor([[1, d // 2, d // 2, 1]], dtype=torch.int32, device=dev)
+    _, on, _ = transitions_device(None, syn, act, d, out_dtype=torch.uint8)
+    return on[0].cpu().numpy().astype(np.int64)
+
+
+def shift_state(row, col, previous_state, state, grid_shift, device="cuda"):
+    """shift_state (src/util.py:97-102; numba twin src/numba/util.py:8-14): both states rolled by
+    (grid_shift-row, grid_shift-col) so that (row,col) lands on (grid_shift,grid_shift)."""
+    prev, st = np.asarray(previous_state), np.asarray(state)
+    d = int(st.shape[-1])
+    if int(grid_shift) != d // 2:
+        raise ValueError("grid_shift must be toric_size // 2")
+    dev = torch.device(device)
+    act = torch.tensor([[0, int(row), int(col), 1]], dtype=torch.int32, device=dev)
+    op, on, _ = transitions_device(_pack(prev[None], d, dev), _pack(st[None], d, dev), act, d,
+                                   out_dtype=torch.uint8)
+    return op[0].cpu().numpy().astype(np.int64), on[0].cpu().numpy().astype(np.int64)
 
 
 def generateTransitionParallel(action, reward, state, next_state, terminal_state, grid_shift, trans_type=None,
