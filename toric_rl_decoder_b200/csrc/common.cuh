@@ -73,6 +73,27 @@ constexpr uint32_t kMaxFixedAttempts = 1u << 10;
 constexpr int kSampleOneDraw = 16;             // TC_SAMPLE_ONE_DRAW (OR-ed into the sampling mode)
 
 // ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch: the three kernels of one actor step (and the first kernel of the next
+// step) are launched with cudaLaunchAttributeProgrammaticStreamSerialization, so a kernel's CTAs become
+// resident while the previous kernel drains and only its reads of the predecessor's results wait.
+// pdl_wait() returns once every prerequisite grid has completed and its writes are visible (a no-op for a
+// normal launch); pdl_launch_dependents() lets the next kernel in the stream start launching.
+// ---------------------------------------------------------------------------------------------
+#ifndef TC_PDL
+#define TC_PDL 1
+#endif
+__device__ __forceinline__ void pdl_wait() {
+#if TC_PDL
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+__device__ __forceinline__ void pdl_launch_dependents() {
+#if TC_PDL
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+#endif
+}
+
+// ---------------------------------------------------------------------------------------------
 // d-bit row helpers
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t row_mask(int d) { return d >= 32 ? 0xffffffffu : ((1u << d) - 1u); }

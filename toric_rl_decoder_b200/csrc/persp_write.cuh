@@ -158,6 +158,8 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     }
     __syncthreads();
   }
+  pdl_wait();                 // offsets / syndromes come from the kernels in front; the table above does not
+  pdl_launch_dependents();
 
   uint32_t ring = 0;                             // staging tiles pushed so far by this warp
   const int64_t stride = (int64_t)gridDim.x * Cfg::kWarps;

@@ -216,6 +216,8 @@ scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) carry_s = 0;
   __syncthreads();
+  pdl_wait();                 // block_sum comes from the kernel in front
+  pdl_launch_dependents();
   for (int64_t base = 0; base < nblocks; base += 1024) {
     const int64_t i = base + tid;
     const long long v = i < nblocks ? (long long)block_sum[i] : 0;
@@ -290,6 +292,8 @@ __global__ void __launch_bounds__(kThreads, 4) actor_step_kernel(const ActorArgs
   const bool valid = e < a.n;
   if (!valid) e = a.n - 1;
   const bool lead = valid && r == 0;
+  pdl_wait();                 // the previous step's perspective writer still reads syn
+  pdl_launch_dependents();
   Rows s;
   load_qubits<G>(a.qubits, e, d, r, s);
   load_syn<G>(a.syn, e, d, r, s);
@@ -379,6 +383,23 @@ inline int launch_status() {
   return err == cudaSuccess ? 0 : (int)err;
 }
 inline unsigned grid_for(int64_t threads, int per_block) { return (unsigned)((threads + per_block - 1) / per_block); }
+// launch with the programmatic-stream-serialization attribute (see common.cuh: pdl_wait / pdl_launch_dependents)
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+                       Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(block, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = TC_PDL ? 1 : 0;
+  cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 inline uint2 make_key(uint64_t seed) { return make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)); }
 
 #define TC_DISPATCH_G(d, CALL)                 \
@@ -439,8 +460,8 @@ void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* p
 #endif
   unsigned grid = grid_for(n, WPB);
   if (TC_WRITE_WAVES > 0 && grid > (unsigned)slots[dev] * TC_WRITE_WAVES) grid = (unsigned)slots[dev] * TC_WRITE_WAVES;
-  persp_write_kernel<D, OutT><<<grid, WPB * 32, Cfg::kSmemBytes, st>>>(syn, w.local_off, w.block_off, w.epb, out,
-                                                                      pos, offsets, overflow, cap, n, one16);
+  launch_pdl(persp_write_kernel<D, OutT>, grid, WPB * 32, Cfg::kSmemBytes, st, syn, (const int32_t*)w.local_off,
+             (const int64_t*)w.block_off, w.epb, out, pos, offsets, overflow, cap, n, one16);
 }
 
 template <typename OutT>
@@ -630,8 +651,9 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
   a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
   a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
   a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d;
-  TC_DISPATCH_G(d, (actor_step_kernel<G><<<(unsigned)w.nblocks, kThreads, 0, st>>>(a)));
-  scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, counters);
+  TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kThreads, 0, st, a)));
+  launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, offsets + n,
+             counters);
   return launch_status();
 }
 

@@ -220,7 +220,8 @@ class ToricEngine:
         if self.out is None:
             self.ensure_capacity(self.worst_case_capacity())
         self._last_syn = self.syn
-        self.overflow.zero_()
+        # `overflow` is sticky here (cleared by perspectives() / perspective_views()): no memset between the
+        # writer of one step and the first kernel of the next, so the launches chain back to back
         if self.out_dtype is not torch.float32:      # fused entry point is float32; same two halves otherwise
             _lib.check(self.lib.tc_actor_pre(
                 _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
