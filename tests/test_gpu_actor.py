@@ -214,7 +214,7 @@ def _torch_reference_perspectives(state, pos, env_of, d):
     return torch.stack((out0, out1), dim=1).float()
 
 
-@pytest.mark.parametrize("d,n", ((7, 65536), (5, 30000), (8, 4096), (4, 8192), (3, 5000), (9, 8192), (15, 4096),
+@pytest.mark.parametrize("d,n", ((7, 65536), (5, 30000), (8, 4096), (4, 8192), (3, 5000), (3, 300001), (9, 8192), (15, 4096),
                                  (25, 1024), (32, 300)))
 def test_full_size_properties(pkg, d, n):
     """BASELINE configs[1] size (d=7, 65536 envs) and the other lattice sizes / both writer code paths: after a

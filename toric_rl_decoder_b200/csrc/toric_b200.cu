@@ -56,12 +56,29 @@ __global__ void pack_state_kernel(const uint8_t* __restrict__ st, uint32_t* __re
   syn[t] = w;
 }
 
-__global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t n) {
-  const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n * 2 * d) return;
-  const uint32_t w = syn[t];
-  uint8_t* dst = st + t * d;
-  for (int j = 0; j < d; ++j) dst[j] = (uint8_t)((w >> j) & 1u);
+// 8 output bytes per thread, written as one 8-byte store: byte b of the flat [n][2][d][d] array is bit b % d of
+// row word b / d
+__global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t total) {
+  const int64_t b0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (b0 >= total) return;
+  int64_t row = b0 / d;
+  int j = (int)(b0 - row * d);
+  uint32_t w = syn[row];
+  uint32_t out[2] = {0u, 0u};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    out[k >> 2] |= ((w >> j) & 1u) << (8 * (k & 3));
+    if (++j == d) {
+      j = 0;
+      ++row;
+      if (b0 + k + 1 < total) w = syn[row];
+    }
+  }
+  if (b0 + 8 <= total && (((uintptr_t)st) & 7) == 0) {
+    *reinterpret_cast<uint2*>(st + b0) = make_uint2(out[0], out[1]);
+  } else {
+    for (int k = 0; k < 8 && b0 + k < total; ++k) st[b0 + k] = (uint8_t)(out[k >> 2] >> (8 * (k & 3)));
+  }
 }
 
 // row words -> np.packbits(state, axis=-1, bitorder="little"): ceil(d/8) bytes per lattice row
@@ -207,52 +224,57 @@ persp_count_kernel(const uint32_t* __restrict__ syn, int32_t* __restrict__ count
   cta_count_prefix<G>(count, valid, r, e, counts, local_off, block_sum);
 }
 
-// single CTA: exclusive scan of the per-CTA sums -> block_off (int64), grand total -> offsets[n]
+// single CTA: exclusive scan of the per-CTA sums -> block_off (int64), grand total -> offsets[n].
+// Warp w owns a contiguous chunk of ceil(nblocks/32) sums and walks it in 32-wide tiles (coalesced 128-byte
+// reads, no CTA barrier inside the loops): pass 1 adds the chunk up, the 32 chunk totals are scanned once,
+// pass 2 re-reads the chunk and writes the running prefix.
 __global__ void __launch_bounds__(1024)
 scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ block_off, int64_t nblocks,
                    int64_t* __restrict__ total_out, int64_t* __restrict__ counters) {
   __shared__ long long warp_tot[32];
-  __shared__ long long carry_s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) carry_s = 0;
-  __syncthreads();
   pdl_wait();                 // block_sum comes from the kernel in front
   pdl_launch_dependents();
-  for (int64_t base = 0; base < nblocks; base += 1024) {
-    const int64_t i = base + tid;
-    const long long v = i < nblocks ? (long long)block_sum[i] : 0;
-    long long inc = v;
+  const int64_t chunk = ((nblocks + 1023) / 1024) * 32;          // multiple of the tile width
+  const int64_t lo = (int64_t)warp * chunk < nblocks ? (int64_t)warp * chunk : nblocks;
+  const int64_t hi = lo + chunk < nblocks ? lo + chunk : nblocks;
+  long long sum = 0;
+#pragma unroll 4
+  for (int64_t i = lo + lane; i < hi; i += 32) sum += (long long)block_sum[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) warp_tot[warp] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    const long long w = warp_tot[lane];
+    long long winc = w;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const long long t = __shfl_up_sync(0xffffffffu, inc, o);
+      const long long t = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += t;
+    }
+    warp_tot[lane] = winc - w;   // exclusive prefix of the chunk totals
+    if (lane == 31) {
+      *total_out = winc;
+      if (counters) atomicAdd(reinterpret_cast<unsigned long long*>(counters + kCtrPerspectives),
+                              (unsigned long long)winc);
+    }
+  }
+  __syncthreads();
+  long long carry = warp_tot[warp];
+  for (int64_t base = lo; base < hi; base += 32) {
+    const int64_t i = base + lane;
+    const int v = i < hi ? block_sum[i] : 0;
+    int inc = v;                 // a tile of 32 CTA sums stays far below 2^31 (<= 32 * 32 * 2 * 32 * 32)
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, inc, o);
       if (lane >= o) inc += t;
     }
-    if (lane == 31) warp_tot[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-      const long long w = warp_tot[lane];
-      long long winc = w;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const long long t = __shfl_up_sync(0xffffffffu, winc, o);
-        if (lane >= o) winc += t;
-      }
-      warp_tot[lane] = winc - w;   // exclusive prefix of the warp totals
-    }
-    __syncthreads();
-    const long long carry = carry_s;
-    if (i < nblocks) block_off[i] = carry + warp_tot[warp] + (inc - v);
-    __syncthreads();
-    if (tid == 1023) carry_s = carry + warp_tot[31] + inc;   // last thread's inclusive value closes the tile
-    __syncthreads();
-  }
-  if (tid == 0) {
-    *total_out = carry_s;
-    if (counters) atomicAdd(reinterpret_cast<unsigned long long*>(counters + kCtrPerspectives),
-                            (unsigned long long)carry_s);
+    if (i < hi) block_off[i] = carry + (long long)(inc - v);
+    carry += (long long)__shfl_sync(0xffffffffu, inc, 31);
   }
 }
-
 
 // ------------------------------------------------------------------------------------------------
 // fused actor iteration: [random action] -> step -> reward/terminal -> bookkeeping / auto-reset -> count
@@ -515,7 +537,8 @@ int tc_pack_state(const uint8_t* state01, uint32_t* syn, int d, int64_t n, void*
 int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, void* stream) {
   if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
   if (n == 0) return 0;
-  unpack_state_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, n);
+  const int64_t total = n * 2 * d * d;
+  unpack_state_kernel<<<grid_for((total + 7) / 8, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, total);
   return launch_status();
 }
 
