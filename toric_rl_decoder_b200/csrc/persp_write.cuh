@@ -101,11 +101,13 @@ __device__ __forceinline__ uint4 expand_chunk(uint32_t bits, uint32_t one16) {
     return make_uint4((bits & 1u) * 0x3f800000u, (bits & 2u) * 0x1fc00000u, (bits & 4u) * 0x0fe00000u,
                       (bits & 8u) * 0x07f00000u);
   } else if constexpr (sizeof(OutT) == 2) {
-    // 8 bits -> 8 halves: two per 32-bit word, one16 = bit pattern of 1.0 (0x3f80 bf16, 0x3c00 fp16)
-    const uint32_t hi = one16 << 15;             // (x & 2) * hi puts 1.0 in the upper half
-    return make_uint4((bits & 1u) * one16 + (bits & 2u) * hi, ((bits >> 2) & 1u) * one16 + ((bits >> 2) & 2u) * hi,
-                      ((bits >> 4) & 1u) * one16 + ((bits >> 4) & 2u) * hi,
-                      ((bits >> 6) & 1u) * one16 + ((bits >> 6) & 2u) * hi);
+    // 8 bits -> 8 halves, two per 32-bit word; one16 = bit pattern of 1.0 (0x3f80 bf16, 0x3c00 fp16).
+    // A nibble times 0x00204081 lands bit k at bit 8k (the partial products do not overlap); a byte permute
+    // then pairs bytes (2k, 2k+1) as the two 0/1 halves of word k, and one multiply scales both halves.
+    const uint32_t lo = ((bits & 15u) * 0x00204081u) & 0x01010101u;
+    const uint32_t hi = (((bits >> 4) & 15u) * 0x00204081u) & 0x01010101u;
+    return make_uint4(__byte_perm(lo, 0u, 0x4140) * one16, __byte_perm(lo, 0u, 0x4342) * one16,
+                      __byte_perm(hi, 0u, 0x4140) * one16, __byte_perm(hi, 0u, 0x4342) * one16);
   } else {
     // 16 bits -> 16 bytes: a nibble times 0x00204081 lands bit k at bit 8k (the four partial products do not overlap)
     return make_uint4(((bits & 15u) * 0x00204081u) & 0x01010101u, (((bits >> 4) & 15u) * 0x00204081u) & 0x01010101u,
