@@ -2,7 +2,7 @@
 """BASELINE.json configs other than the headline (configs[1] is bench.py), run at bounded sizes on one GPU.
 Prints one JSON line per config; the driver-facing numbers stay in bench.py.
 
-  python scripts/run_configs.py [--only c1,c3,c4,c5] [--scale 1.0]
+  python scripts/run_configs.py [--only c1,c2,c3,c4,c5] [--scale 1.0]
 """
 import argparse
 import json
@@ -52,6 +52,49 @@ def c1(scale):
         emit(config="c1 d=5 p=0.1 greedy NN_11 (fp32, TF32 off)", episodes=n, success=float(ec[0]),
              ground_state=float(gs[0]), mean_steps=float(steps[0]), mean_q=float(mq[0]),
              env_steps_per_s=float(steps[0]) * n / wall, seconds=wall)
+
+
+def c2(scale):
+    """configs[1]: d=7, p=0.1, 65536 envs, seeds {0,1,2}.  Two variants: the actor loop with
+    random actions (what bench.py times) and "fresh syndromes only" (reset + perspectives of the new syndromes)."""
+    d, n = 7, int(65536 * scale)
+    per_persp = 8 * d * d + 4
+    for seed in (0, 1, 2):
+        eng = pkg.ToricEngine(d, n, seed=seed, p_error=0.1)
+        eng.ensure_capacity(eng.worst_case_capacity())
+        eng.reset()
+        for _ in range(20):
+            eng.actor_step()
+        c0 = eng.read_counters()
+        steps = 200
+
+        def loop():
+            for _ in range(steps):
+                eng.actor_step()
+        _, dt = gpu_time(loop)
+        c = eng.read_counters()
+        sum_p = c["perspectives"] - c0["perspectives"]
+        emit(config="c2 actor loop, random actions", d=d, envs=n, seed=seed, steps=steps,
+             mean_perspectives_per_env=sum_p / (n * steps), env_steps_per_s=n * steps / dt,
+             step_GBps=(sum_p * per_persp + n * steps * 154) / dt / 1e9, ms_per_step=1e3 * dt / steps)
+        eng.reset()
+        eng.perspectives()
+        iters = 100
+        tot = torch.zeros((), dtype=torch.int64, device="cuda")
+
+        def fresh():
+            for _ in range(iters):
+                eng.reset()
+                eng.perspectives()
+                tot.add_(eng.offsets[n])
+        fresh()                                   # warm-up
+        tot.zero_()
+        _, dt = gpu_time(fresh)
+        sum_p = int(tot.item())
+        emit(config="c2 fresh syndromes only (reset + perspectives)", d=d, envs=n, seed=seed, iters=iters,
+             mean_perspectives_per_env=sum_p / (n * iters), syndromes_per_s=n * iters / dt,
+             GBps=(sum_p * per_persp + n * iters * (168 + 56 + 26 + 8)) / dt / 1e9, ms_per_iter=1e3 * dt / iters)
+        del eng
 
 
 def c3(scale):
@@ -114,7 +157,10 @@ def c4(scale):
 def c5(scale):
     """configs[4]: large-lattice stress.  Env state for the whole shard stays resident; the perspective tensor
     is produced in env chunks sized to the output buffer (the consumer reads it between chunks)."""
+    only_d = os.environ.get("C5_ONLY_D")
     for d, p in ((15, 0.05), (15, 0.1), (15, 0.2), (25, 0.05), (25, 0.1), (25, 0.2)):
+        if only_d and int(only_d) != d:
+            continue
         n = int((1 << 17) * scale) if d == 15 else int((1 << 15) * scale)
         eng = pkg.ToricEngine(d, n, seed=9, p_error=p)
         budget = 24 << 30
@@ -154,13 +200,13 @@ def c5(scale):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--only", default="c1,c3,c4,c5")
+    ap.add_argument("--only", default="c1,c2,c3,c4,c5")
     ap.add_argument("--scale", type=float, default=1.0)
     a = ap.parse_args()
     emit(gpu=torch.cuda.get_device_name(0), torch=torch.__version__)
     for name in a.only.split(","):
         try:
-            {"c1": c1, "c3": c3, "c4": c4, "c5": c5}[name](a.scale)
+            {"c1": c1, "c2": c2, "c3": c3, "c4": c4, "c5": c5}[name](a.scale)
         except Exception as ex:  # keep going: each config is independent
             emit(config=name, error=repr(ex))
 

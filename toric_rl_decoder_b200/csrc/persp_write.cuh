@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
 persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
                    const int64_t* __restrict__ block_off, int epb, OutT* __restrict__ out,
                    uint8_t* __restrict__ pos, int64_t* __restrict__ offsets, int32_t* __restrict__ overflow,
-                   int64_t cap, int64_t n, uint32_t one16) {
+                   int64_t cap, int64_t n, uint32_t one16, int split) {
   using Cfg = PerspCfg<D>;
   using OC = OutCfg<OutT>;
   constexpr int kE = OC::kE;
@@ -165,7 +165,13 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
 
   uint32_t ring = 0;                             // staging tiles pushed so far by this warp
   const int64_t stride = (int64_t)gridDim.x * Cfg::kWarps;
-  for (int64_t e = (int64_t)blockIdx.x * Cfg::kWarps + warp; e < n; e += stride) {
+  // work item = (env, slice): with split > 1 the tiles of one env are divided among `split` warps (large
+  // lattices: an env is hundreds of tiles, and few long CTAs would leave the last wave half empty); slice 0
+  // also writes the env's positions and offset
+  const int64_t n_items = n * split;
+  for (int64_t item = (int64_t)blockIdx.x * Cfg::kWarps + warp; item < n_items; item += stride) {
+    const int64_t e = split == 1 ? item : item / split;
+    const int slice = split == 1 ? 0 : (int)(item - e * split);
     uint32_t v = 0, pl = 0;
     if (lane < D) {
       v = __ldg(syn + e * 2 * D + lane);
@@ -177,12 +183,13 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
     const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
     off = __shfl_sync(kFull, off, 0);
-    if (lane == 0) offsets[e] = off;
+    if (lane == 0 && slice == 0) offsets[e] = off;
     if (P == 0) continue;
     if (off + P > cap) {
       if (lane == 0 && overflow) *overflow = 1;
       continue;
     }
+    uint8_t* const pos_w = slice == 0 ? pos : nullptr;
 
     // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
     // One candidate qubit per lane and round; selected candidates are compacted in order with a ballot.
@@ -201,7 +208,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
           if (sel) {
             const int k = kbase + __popc(bal & ((1u << lane) - 1u));
             sp[k] = (uint16_t)cd.x;
-            if (pos) pos32[off + k] = cd.y;
+            if (pos_w) pos32[off + k] = cd.y;
           }
           kbase += __popc(bal);
         } else {
@@ -217,7 +224,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
             int rj = m ? G - j : j - G; if (rj < 0) rj += D;
             const int r0 = m ? rj : ia, r1 = m ? ia : rj;
             sp[k] = (uint16_t)(m | (r0 << 1) | (r1 << 6));
-            if (pos) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
+            if (pos_w) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
           }
           kbase += __popc(bal);
         }
@@ -338,7 +345,11 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       return word;
     };
 
-    for (int t = 0; t < nT; ++t, ++ring) {
+    // contiguous tile range per slice (measured: dealing the tiles round-robin to the slices is 15 % SLOWER than
+    // one warp per env at d=25, contiguous ranges are 10 % faster -- profiles/r01_writer_split_d25.txt)
+    const int t_begin = (int)((int64_t)nT * slice / split);
+    const int t_end = (int)((int64_t)nT * (slice + 1) / split);
+    for (int t = t_begin; t < t_end; ++t, ++ring) {
       uint32_t word[kWordsPerLane];
 #pragma unroll
       for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);

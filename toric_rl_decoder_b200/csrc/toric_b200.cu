@@ -480,10 +480,28 @@ void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* p
 #ifndef TC_WRITE_WAVES
 #define TC_WRITE_WAVES 0
 #endif
-  unsigned grid = grid_for(n, WPB);
+  // TC_WRITE_SPLIT: warps per env on the row path (d > 8), where one env is tens to hundreds of 4 KB tiles:
+  // enough (env, slice) items for >= 8 waves of CTAs, at most 16 slices and never more slices than an env of
+  // average density has tiles.  The plane path (d <= 8: ~6 tiles per env, setup-heavy) keeps one warp per env.
+#ifndef TC_WRITE_SPLIT
+#define TC_WRITE_SPLIT 0          /* 0 = automatic */
+#endif
+  int split = 1;
+  if (!Cfg::kPlane) {
+    if (TC_WRITE_SPLIT > 0) {
+      split = TC_WRITE_SPLIT;
+    } else {
+      const int64_t ctas = (n + WPB - 1) / WPB;
+      const int64_t want = ((int64_t)slots[dev] * 8 + ctas - 1) / ctas;
+      const int tiles = (D * D / 2) * 2 * D * D * (int)sizeof(OutT) / kTileBytes;   // env with P = d^2/2
+      split = (int)(want < 1 ? 1 : (want > 16 ? 16 : want));
+      if (split > tiles) split = tiles > 1 ? tiles : 1;
+    }
+  }
+  unsigned grid = grid_for(n * split, WPB);
   if (TC_WRITE_WAVES > 0 && grid > (unsigned)slots[dev] * TC_WRITE_WAVES) grid = (unsigned)slots[dev] * TC_WRITE_WAVES;
   launch_pdl(persp_write_kernel<D, OutT>, grid, WPB * 32, Cfg::kSmemBytes, st, syn, (const int32_t*)w.local_off,
-             (const int64_t*)w.block_off, w.epb, out, pos, offsets, overflow, cap, n, one16);
+             (const int64_t*)w.block_off, w.epb, out, pos, offsets, overflow, cap, n, one16, split);
 }
 
 template <typename OutT>
