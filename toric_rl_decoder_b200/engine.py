@@ -202,12 +202,15 @@ class ToricEngine:
                                            self.workspace.numel(), self.d, n, _stream()), "tc_persp_count")
 
     def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
-                   freeze_done=False, actions_buffer=None):
+                   freeze_done=False, actions_buffer=None, results=None):
         """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
         self.actions itself (e.g. filled by select_action) skips the copy; actions_buffer (device int32
         (n,4), 16-byte aligned) is read in place instead of self.actions.  freeze_done leaves envs whose
-        syndrome is already trivial untouched (batched evaluation)."""
+        syndrome is already trivial untouched (batched evaluation).  results = (reward f32 (n,), terminal u8
+        (n,), counts i32 (n,)) device tensors to receive this step's results instead of self.reward /
+        self.terminal / self.counts (HostActorPipeline points them into its download block)."""
         flags = (ACTOR_AUTO_RESET if auto_reset else 0) | (ACTOR_FREEZE_DONE if freeze_done else 0)
+        reward, terminal, counts = results if results is not None else (self.reward, self.terminal, self.counts)
         act_buf = self.actions
         if actions_buffer is not None:
             act_buf = actions_buffer
@@ -225,17 +228,17 @@ class ToricEngine:
         if self.out_dtype is not torch.float32:      # fused entry point is float32; same two halves otherwise
             _lib.check(self.lib.tc_actor_pre(
                 _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
-                _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+                _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
                 _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
-                int(n_fixed), self.seed, self.env_base, _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace),
+                int(n_fixed), self.seed, self.env_base, _ptr(counts), _ptr(self.offsets), _ptr(self.workspace),
                 self.workspace.numel(), self.d, self.n, _stream()), "tc_actor_pre")
             self.persp_write()
             return
         _lib.check(self.lib.tc_actor_step(
             _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
-            _ptr(self.reward), _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+            _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
             _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
-            int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(self.counts),
+            int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(counts),
             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace), self.workspace.numel(),
             self.d, self.n, _stream()), "tc_actor_step")
 

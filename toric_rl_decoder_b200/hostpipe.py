@@ -90,10 +90,9 @@ class HostActorPipeline:
             slot["d_actions"].copy_(actions_host, non_blocking=True)
             slot["ev_actions"].record(self.h2d_stream)
         compute.wait_event(slot["ev_actions"])
-        eng.actor_step(auto_reset=auto_reset, actions_buffer=slot["d_actions"])
-        slot["d_reward"].copy_(eng.reward, non_blocking=True)
-        slot["d_counts"].copy_(eng.counts, non_blocking=True)
-        slot["d_term"].copy_(eng.terminal, non_blocking=True)
+        # the step writes reward / terminal / counts straight into the slot's download block
+        eng.actor_step(auto_reset=auto_reset, actions_buffer=slot["d_actions"],
+                       results=(slot["d_reward"], slot["d_term"], slot["d_counts"]))
         if self.states == "u8":
             _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
                                                compute.cuda_stream), "tc_unpack_state")
