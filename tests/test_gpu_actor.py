@@ -284,3 +284,25 @@ def test_host_pipeline_matches_oracle(pkg, d, states):
             assert "states" not in got[k] and "state_rows" not in got[k]
         _, _, counts, _ = O.perspectives_batch(s)
         assert (got[k]["counts"] == counts).all()
+
+
+@pytest.mark.parametrize("d,n", ((7, 3000), (15, 200)))
+def test_cuda_graph_replay_equals_eager(pkg, d, n):
+    """k fused steps captured into a CUDA graph (PDL edges included) and replayed == the same steps launched
+    eagerly: states, counters, perspectives."""
+    a = pkg.ToricEngine(d, n, seed=11, p_error=0.1, max_steps=6)
+    b = pkg.ToricEngine(d, n, seed=11, p_error=0.1, max_steps=6)
+    for e in (a, b):
+        e.reset()
+    for _ in range(20):
+        a.actor_step()
+    g = b.capture_actor_steps(5)
+    for _ in range(4):
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(a.qubits, b.qubits) and torch.equal(a.syn, b.syn)
+    assert torch.equal(a.steps, b.steps) and torch.equal(a.episode, b.episode)
+    assert torch.equal(a.counters, b.counters)
+    pa, pb = a.perspective_views(), b.perspective_views()
+    for x, y in zip(pa, pb):
+        assert torch.equal(x, y)

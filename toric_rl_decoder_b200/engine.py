@@ -242,6 +242,25 @@ class ToricEngine:
             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace), self.workspace.numel(),
             self.d, self.n, _stream()), "tc_actor_step")
 
+    def capture_actor_steps(self, k=1, **kwargs):
+        """Capture k fused actor steps (actor_step(**kwargs), device-drawn actions by default) into one CUDA
+        graph and return it; `graph.replay()` then advances every env by k steps with a single launch -- for
+        small batches, where three kernel launches per step are launch-bound.  Capturing runs nothing, so the
+        env state is unchanged; the programmatic-dependent-launch edges between the kernels are kept."""
+        if kwargs.get("actions") is not None and kwargs["actions"] is not self.actions:
+            raise ValueError("a captured step reads self.actions (fill it in place) or draws actions on device")
+        if self.out is None:
+            self.ensure_capacity(self.worst_case_capacity())
+        if kwargs.get("keep_prev") and self.prev_syn is None:
+            self.prev_syn = torch.zeros_like(self.syn)
+        self.perspectives()            # first-launch setup of the writer (function attributes) outside the capture
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for _ in range(int(k)):
+                self.actor_step(**kwargs)
+        return graph
+
     def actor_pre(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0):
         """First half of actor_step (step / bookkeeping / count / scan) -- used with persp_write() by
         callers that time the two halves separately (bench.py)."""
