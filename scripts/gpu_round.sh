@@ -18,4 +18,9 @@ timeout 300 $NCU_CMD > gpurun_out/plain2.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:persp_write -s 81 -c 2 -o gpurun_out/prof_write -f $NCU_CMD > gpurun_out/ncu_full.log 2>&1
 timeout 300 $NCU_CMD > gpurun_out/plain3.log 2>&1 &&
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:actor_step -s 81 -c 2 -o gpurun_out/prof_actor -f $NCU_CMD > gpurun_out/ncu_full2.log 2>&1
+timeout 300 python scripts/kernel_table.py > gpurun_out/kernel_table.jsonl 2> gpurun_out/kernel_table.err
+timeout 900 python scripts/run_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err
+for dt in bfloat16 float16 uint8; do
+  timeout 300 python bench.py --out-dtype $dt --no-cpu-baseline > gpurun_out/bench_$dt.json 2> gpurun_out/bench_$dt.err
+done
 ls -la gpurun_out

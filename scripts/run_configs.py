@@ -102,7 +102,9 @@ def c3(scale):
     (.MISSING_LARGE_BLOBS), so the weights are seeded random-init: rates are NOT comparable with RL_9.txt."""
     d = 9
     torch.manual_seed(0)
-    model = networks.NN_17(d, 3).cuda().eval().to(memory_format=torch.channels_last)
+    # channel counts padded to a multiple of 8 with zero weights: same function, tensor-core aligned convolutions
+    # (profiles/r01_net_forward.jsonl: 2.9e5 -> 4.6e5 perspectives/s under bf16 autocast)
+    model = networks.pad_channels(networks.NN_17(d, 3).cuda().eval(), 8).to(memory_format=torch.channels_last)
     cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
     n = int(2048 * scale)
 
@@ -131,7 +133,7 @@ def c4(scale):
     + depolarizing p on the rest, results/small_p_error_test.py) and Size_7_NN_11_random weights."""
     d = 7
     model = networks.load_state(networks.NN_11(d, 3), os.path.join(GOLD, "Size_7_NN_11_random_state.pt"), device="cuda")
-    model = model.to(memory_format=torch.channels_last)
+    model = networks.pad_channels(model, 8).to(memory_format=torch.channels_last)
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}

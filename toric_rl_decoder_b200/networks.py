@@ -67,6 +67,38 @@ def load_state(model, path_or_state, device=None):
     return model.eval()
 
 
+def pad_channels(model, multiple=8):
+    """A ConvDecoder with every hidden channel count rounded up to `multiple` and the extra weights zero:
+    the same function (a zero-weight, zero-bias channel is relu(0) = 0 and feeds zero weights), but every
+    convolution is tensor-core aligned -- the reference's schedules (251, 233, 229, 111, 103, 73, 71 ...) are
+    not, which drops cuDNN to its slow paths under TF32 / bf16.  For evaluation throughput only; parity tests
+    use the unpadded network."""
+    chans = CHANNELS[model.arch]
+    up = [((c + multiple - 1) // multiple) * multiple for c in chans]
+    dev = next(model.parameters()).device
+    out = ConvDecoder.__new__(ConvDecoder)
+    nn.Module.__init__(out)
+    out.arch, out.system_size, out.depth, out.device = model.arch, model.system_size, model.depth, model.device
+    cin_old, cin_new = 2, 2
+    with torch.no_grad():
+        for k, (c_old, c_new) in enumerate(zip(chans, up), start=1):
+            src = getattr(model, "conv%d" % k)
+            conv = nn.Conv2d(cin_new, c_new, kernel_size=3, stride=1, padding=src.padding)
+            conv.weight.zero_()
+            conv.bias.zero_()
+            conv.weight[:c_old, :cin_old] = src.weight
+            conv.bias[:c_old] = src.bias
+            setattr(out, "conv%d" % k, conv)
+            cin_old, cin_new = c_old, c_new
+        side = model.system_size - 2
+        lin = nn.Linear(cin_new * side * side, model.linear1.out_features)
+        lin.weight.zero_()
+        lin.weight.view(-1, cin_new, side, side)[:, :cin_old] = model.linear1.weight.view(-1, cin_old, side, side)
+        lin.bias.copy_(model.linear1.bias)
+        out.linear1 = lin
+    return out.to(dev).eval()
+
+
 def strict_fp32():
     """Q-value parity (1e-5 relative, north_star) needs true fp32 convolutions: TF32 off."""
     torch.backends.cuda.matmul.allow_tf32 = False
