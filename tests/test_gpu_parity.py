@@ -243,3 +243,27 @@ def test_perspective_element_types(pkg, d, n, dtype):
         e.actor_step()
     a, b = e32.perspective_views(), e16.perspective_views()
     assert torch.equal(a[0], b[0].float()) and torch.equal(a[1], b[1]) and torch.equal(a[3], b[3])
+
+
+def test_empty_batch(pkg):
+    """Zero environments is a legal batch everywhere (EnvSet(env, 0) in the reference gives empty arrays)."""
+    d = 5
+    envs = pkg.EnvSetB200({"size": d, "p_error": 0.1}, 0)
+    assert envs.resetAll().shape == (0, 2, d, d)
+    st, rw, tm, _ = envs.step(np.zeros((0, 4), dtype=np.int64))
+    assert st.shape == (0, 2, d, d) and rw.shape == (0,) and tm.shape == (0,)
+    assert envs.resetTerminalEnvs(np.zeros(0, dtype=np.int64)).shape == (0, 2, d, d)
+    eng = envs.engine
+    eng.actor_step()
+    eng.ground_state()
+    persp, pos, counts, offsets = eng.perspective_views()
+    assert persp.shape == (0, 2, d, d) and pos.shape[0] == 0 and counts.shape == (0,)
+    assert offsets.cpu().tolist() == [0]
+    out = pkg.generatePerspectiveBatch(d // 2, d, np.zeros((0, 2, d, d), dtype=np.int64))
+    assert out[0].shape[0] == 0
+    # a batch in which no env has a defect: all counts zero, nothing written
+    eng2 = pkg.ToricEngine(d, 9)
+    eng2.set_qubits(np.zeros((9, 2, d, d), np.uint8))
+    eng2.perspectives()
+    p2, _, c2, o2 = eng2.perspective_views()
+    assert p2.shape[0] == 0 and (c2 == 0).all() and (o2 == 0).all()

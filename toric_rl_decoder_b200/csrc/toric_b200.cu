@@ -532,45 +532,51 @@ int tc_workspace_bytes(int d, int64_t n, size_t* out_bytes) {
 }
 
 int tc_pack_qubits(const uint8_t* codes, uint32_t* qubits, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !codes || !qubits) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!codes || !qubits) return -1;
   pack_qubits_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(codes, qubits, d, n);
   return launch_status();
 }
 
 int tc_unpack_qubits(const uint32_t* qubits, uint8_t* codes, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !codes || !qubits) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!codes || !qubits) return -1;
   unpack_qubits_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(qubits, codes, d, n);
   return launch_status();
 }
 
 int tc_pack_state(const uint8_t* state01, uint32_t* syn, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!state01 || !syn) return -1;
   pack_state_kernel<<<grid_for(n * 2 * d, 256), 256, 0, (cudaStream_t)stream>>>(state01, syn, d, n);
   return launch_status();
 }
 
 int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !state01 || !syn) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!state01 || !syn) return -1;
   const int64_t total = n * 2 * d * d;
   unpack_state_kernel<<<grid_for((total + 7) / 8, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, total);
   return launch_status();
 }
 
 int tc_state_rows(const uint32_t* syn, uint8_t* rows, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !rows || !syn) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!rows || !syn) return -1;
   const int nb = (d + 7) / 8;
   state_rows_kernel<<<grid_for(n * 2 * d * nb, 256), 256, 0, (cudaStream_t)stream>>>(syn, rows, d, nb, n);
   return launch_status();
 }
 
 int tc_syndrome(const uint32_t* qubits, uint32_t* syn, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !qubits || !syn) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!qubits || !syn) return -1;
   TC_DISPATCH_G(d, (syndrome_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                        qubits, syn, d, n)));
   return launch_status();
@@ -578,9 +584,10 @@ int tc_syndrome(const uint32_t* qubits, uint32_t* syn, int d, int64_t n, void* s
 
 int tc_step(uint32_t* qubits, uint32_t* syn, const int32_t* actions, float* reward, uint8_t* terminal,
             uint8_t* status, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !qubits || !syn || !actions || !reward || !terminal) return -1;
-  if ((uintptr_t)actions & 15) return -1;
+  if (bad_d(d) || n < 0) return -1;
   if (n == 0) return 0;
+  if (!qubits || !syn || !actions || !reward || !terminal) return -1;
+  if ((uintptr_t)actions & 15) return -1;
   TC_DISPATCH_G(d, (step_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                        qubits, syn, actions, reward, terminal, status, d, n)));
   return launch_status();
@@ -589,10 +596,11 @@ int tc_step(uint32_t* qubits, uint32_t* syn, const int32_t* actions, float* rewa
 int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, const uint32_t* p_thresh,
              uint32_t* episode, const int64_t* idx, int64_t n_idx, int mode, int n_fixed, uint64_t seed,
              int64_t env_base, int d, void* stream) {
-  if (bad_d(d) || n_idx < 0 || !qubits || !syn || !p_thresh || !episode) return -1;
   const int base_mode = mode & ~TC_SAMPLE_ONE_DRAW;
+  if (bad_d(d) || n_idx < 0) return -1;
   if (base_mode < 0 || base_mode > 2 || n_fixed < 0 || (base_mode != 0 && n_fixed == 0)) return -1;
   if (n_idx == 0) return 0;
+  if (!qubits || !syn || !p_thresh || !episode) return -1;
   TC_DISPATCH_G(d, (reset_kernel<G><<<grid_for(n_idx * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                        qubits, syn, gs, status, p_thresh, episode, idx, n_idx, mode, n_fixed, make_key(seed),
                        env_base, d)));
@@ -600,8 +608,9 @@ int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, cons
 }
 
 int tc_ground_state(const uint32_t* qubits, uint8_t* gs, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !qubits || !gs) return -1;
-  if (n == 0) return 0;
+  if (bad_d(d) || n < 0) return -1;
+  if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
+  if (!qubits || !gs) return -1;
   TC_DISPATCH_G(d, (ground_state_kernel<G><<<grid_for(n * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                        qubits, gs, d, n)));
   return launch_status();
@@ -609,14 +618,15 @@ int tc_ground_state(const uint32_t* qubits, uint8_t* gs, int d, int64_t n, void*
 
 int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void* workspace,
                    size_t workspace_bytes, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !syn || !counts || !offsets || !workspace) return -1;
-  const Workspace w = carve(workspace, d, n);
-  if (workspace_bytes < w.bytes) return -2;
+  if (bad_d(d) || n < 0 || !offsets) return -1;
   cudaStream_t st = (cudaStream_t)stream;
-  if (n == 0) {
+  if (n == 0) {               // empty batch: offsets = [0], nothing else is touched
     cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
     return launch_status();
   }
+  if (!syn || !counts || !workspace) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
   TC_DISPATCH_G(d, (persp_count_kernel<G><<<(unsigned)w.nblocks, kThreads, 0, st>>>(syn, counts, w.local_off,
                                                                                     w.block_sum, d, n)));
   scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, nullptr);
@@ -626,8 +636,10 @@ int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void*
 int tc_persp_write_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* pos, int64_t* offsets,
                       int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
                       void* stream) {
-  if (bad_d(d) || n < 0 || cap < 0 || !syn || !offsets || !workspace) return -1;
+  if (bad_d(d) || n < 0 || cap < 0) return -1;
   if (out_dtype < TC_DTYPE_F32 || out_dtype > TC_DTYPE_F16) return -1;
+  if (n == 0) return 0;
+  if (!syn || !offsets || !workspace) return -1;
   if (cap > 0 && !out) return -1;
   if (((uintptr_t)out & 15) || ((uintptr_t)pos & 3)) return -1;
   const Workspace w = carve(workspace, d, n);
@@ -674,18 +686,19 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
                  const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
                  uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
                  size_t workspace_bytes, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode ||
-      !p_thresh || !counts || !offsets || !workspace)
-    return -1;
+  if (bad_d(d) || n < 0 || !offsets) return -1;
   if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
-  if ((uintptr_t)actions & 15) return -1;
-  const Workspace w = carve(workspace, d, n);
-  if (workspace_bytes < w.bytes) return -2;
   cudaStream_t st = (cudaStream_t)stream;
   if (n == 0) {
     cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
     return launch_status();
   }
+  if (!qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode || !p_thresh || !counts ||
+      !workspace)
+    return -1;
+  if ((uintptr_t)actions & 15) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
   ActorArgs a;
   a.qubits = qubits; a.syn = syn; a.prev_syn = prev_syn; a.actions = actions; a.reward = reward;
   a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
@@ -717,9 +730,10 @@ int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* o
                      const int32_t* steps, const uint32_t* eps_thresh, uint32_t eps_scalar,
                      const uint8_t* greedy_in, uint64_t seed, int64_t env_base, int32_t* actions, float* q_sel,
                      int64_t* sel_idx, uint8_t* was_greedy, int64_t n, void* stream) {
-  if (n < 0 || !q_values || !pos || !offsets || !actions || !q_sel) return -1;
-  if (((uintptr_t)actions & 15) || ((uintptr_t)pos & 3)) return -1;
+  if (n < 0) return -1;
   if (n == 0) return 0;
+  if (!q_values || !pos || !offsets || !actions || !q_sel) return -1;
+  if (((uintptr_t)actions & 15) || ((uintptr_t)pos & 3)) return -1;
   select_action_kernel<<<grid_for(n * 32, 256), 256, 0, (cudaStream_t)stream>>>(
       q_values, pos, offsets, episode, steps, eps_thresh, eps_scalar, greedy_in, make_key(seed), env_base, actions,
       q_sel, sel_idx, was_greedy, n);
@@ -728,11 +742,12 @@ int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* o
 
 int tc_transitions(const uint32_t* syn_prev, const uint32_t* syn_next, const int32_t* actions, void* out_prev,
                    void* out_next, int32_t* action_out, int out_dtype, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !actions) return -1;
-  if ((out_prev && !syn_prev) || (out_next && !syn_next)) return -1;
-  if (((uintptr_t)actions & 15) || ((uintptr_t)action_out & 15)) return -1;
+  if (bad_d(d) || n < 0) return -1;
   if (out_dtype != TC_DTYPE_F32 && out_dtype != TC_DTYPE_U8) return -1;
   if (n == 0) return 0;
+  if (!actions) return -1;
+  if ((out_prev && !syn_prev) || (out_next && !syn_next)) return -1;
+  if (((uintptr_t)actions & 15) || ((uintptr_t)action_out & 15)) return -1;
   const unsigned grid = grid_for(n * 2 * d * d, 256);
   cudaStream_t st = (cudaStream_t)stream;
   if (out_dtype == TC_DTYPE_F32)
@@ -746,8 +761,9 @@ int tc_transitions(const uint32_t* syn_prev, const uint32_t* syn_next, const int
 
 int tc_td_priorities(const int32_t* actions, const float* reward, const float* q, const float* q_next,
                      float discount, float* priorities, int64_t n, void* stream) {
-  if (n < 0 || !actions || !reward || !q || !q_next || !priorities) return -1;
+  if (n < 0) return -1;
   if (n == 0) return 0;
+  if (!actions || !reward || !q || !q_next || !priorities) return -1;
   td_priority_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(actions, reward, q, q_next, discount,
                                                                         priorities, n);
   return launch_status();
@@ -755,8 +771,9 @@ int tc_td_priorities(const int32_t* actions, const float* reward, const float* q
 
 int tc_segmented_max(const float* q_values, const int64_t* offsets, int pad_to, const int32_t* pad_to_dev,
                      float* out, int64_t n, void* stream) {
-  if (n < 0 || !q_values || !offsets || !out) return -1;
+  if (n < 0) return -1;
   if (n == 0) return 0;
+  if (!q_values || !offsets || !out) return -1;
   segmented_max_kernel<<<grid_for(n * 32, 256), 256, 0, (cudaStream_t)stream>>>(q_values, offsets, pad_to,
                                                                                pad_to_dev, out, n);
   return launch_status();
