@@ -93,6 +93,25 @@ __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, int byt
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
+// One lane of the (converged) warp, the same one on every call: the bulk async-groups it commits are per-thread
+// state, and ptxas knows a single thread is active behind elect.sync, so the uniform-register operands of UBLKCP
+// need no per-lane waterfall loop (with `if (lane == 0)` it emits one).
+__device__ __forceinline__ bool elect_one() {
+#ifdef TC_NO_ELECT
+  return (threadIdx.x & 31) == 0;
+#else
+  uint32_t is_leader;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(is_leader));
+  return is_leader != 0;
+#endif
+}
+
 // kE stream bits -> one 16-byte chunk of output elements
 template <typename OutT>
 __device__ __forceinline__ uint4 expand_chunk(uint32_t bits, uint32_t one16) {
@@ -290,8 +309,23 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
 
     // ---- bit stream -> output tiles -> TMA bulk stores ----
     const int64_t f_start = off * (int64_t)(2 * DD);
-    const int ph = (int)(f_start & (kE - 1));    // phantom elements in front (owned by the previous env); even
-    OutT* __restrict__ base = out + (f_start - ph);    // 16-byte aligned
+    // phantom elements in front (owned by the previous env; even): the stream starts at the kAlignBytes boundary
+    // below the env's first element, so every tile boundary after the first is aligned to it in global memory.
+    // Whole 128-byte lines per TMA store are worth +0.6 % (d=7) to +1.1 % (d=9) where the writer is HBM-bound
+    // (float32, d >= 6); where it is instruction-bound (small d, narrow elements) the up-to-31 extra phantom
+    // elements cost 1-2 %, so those keep the minimal 16-byte alignment (profiles/r01_writer_variants.txt).
+#ifdef TC_ALIGN_BYTES
+    constexpr int kAlignBytes = TC_ALIGN_BYTES;
+#else
+    constexpr int kAlignBytes = (OC::kB == 4 && D >= 6) ? 128 : 16;
+#endif
+    constexpr int kAlignElems = kAlignBytes / OC::kB;
+    static_assert(kAlignElems >= kE, "alignment below one 16-byte chunk");
+    constexpr int kShiftPlanes = (kAlignElems + DD - 1) / DD;   // empty planes in front so that gg below is >= 0
+    const int ph = (int)(f_start & (kAlignElems - 1));
+    const int phc = ph & ~(kE - 1);              // start of the 16-byte chunk holding the first own element
+    const int phr = ph - phc;                    // own elements start phr into that chunk (partial if != 0)
+    OutT* __restrict__ base = out + (f_start - ph);
     const int F = P * 2 * DD;                    // >= 18 > kE, so head and tail chunks are never the same chunk
     const int L = F + ph;
     const int nW = (L + 31) >> 5;
@@ -303,12 +337,12 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       if (W < nW) {
         if constexpr (Cfg::kPlane) {
           const unsigned long long* planes = reinterpret_cast<const unsigned long long*>(tab_raw);
-          const int gg = 32 * W - ph + DD;       // shifted by one (empty) plane so that it is never negative
+          const int gg = 32 * W - ph + kShiftPlanes * DD;   // shifted by empty planes: never negative
           const int kk = gg / DD;
-          const int r = gg - kk * DD;            // first stream bit of the word inside plane kk-1
+          const int r = gg - kk * DD;            // first stream bit of the word inside plane kk - kShiftPlanes
 #pragma unroll
           for (int j = 0; j < Cfg::kPlanesPerWord; ++j) {
-            const int k = kk - 1 + j;            // plane k = perspective k>>1, syndrome plane k&1
+            const int k = kk - kShiftPlanes + j;  // plane k = perspective k>>1, syndrome plane k&1
             const int sh = j * DD - r;
             if (k >= 0 && k < 2 * P && sh < 32) {
               const unsigned long long pv = planes[(int)sp[k >> 1] + (k & 1) * DD];
@@ -355,7 +389,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
       OutT* st = stage + (ring % kStageBufs) * kTileElems;
       if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
+        if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
         __syncwarp();
       }
       uint4* st4 = reinterpret_cast<uint4*>(st);
@@ -374,13 +408,13 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       // partial 16-byte chunks (shared with the neighbouring envs) go out as element pairs: head on lanes
       // 0..kE/2-1, tail on lanes 8..8+kE/2-1
       using PairT = typename OC::PairT;
-      if (t == 0 && ph && lane < kE / 2 && 2 * lane >= ph)
-        __stcs(reinterpret_cast<PairT*>(base) + lane, reinterpret_cast<const PairT*>(st)[lane]);
+      if (t == 0 && phr && lane < kE / 2 && 2 * lane >= phr)
+        __stcs(reinterpret_cast<PairT*>(base + phc) + lane, reinterpret_cast<const PairT*>(st + phc)[lane]);
       if (t == nT - 1 && lane >= 8 && 2 * (lane - 8) < L - L16)
         __stcs(reinterpret_cast<PairT*>(base + L16) + (lane - 8),
                reinterpret_cast<const PairT*>(st + (L16 - f0))[lane - 8]);
-      if (lane == 0) {
-        const int lo = (t == 0 && ph) ? kE : 0;
+      if (elect_one()) {
+        const int lo = t == 0 ? (phr ? phc + kE : phc) : 0;
         int hi = L16 - f0;
         if (hi > kTileElems) hi = kTileElems;
         if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * OC::kB);
@@ -389,7 +423,8 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     }
     __syncwarp();
   }
-  if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  __syncwarp();
+  if (elect_one()) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 }  // namespace tc
