@@ -41,11 +41,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--ds", default="5,7,9,15,25")
     ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--scale", type=int, default=1, help="multiply the env counts (asymptotic bandwidth)")
     a = ap.parse_args()
     pk = peak()
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
     for d in [int(x) for x in a.ds.split(",")]:
-        n = (1 << 20) if d <= 9 else ((1 << 18) if d <= 16 else (1 << 16))
+        n = a.scale * ((1 << 20) if d <= 9 else ((1 << 18) if d <= 16 else (1 << 16)))
         eng = pkg.ToricEngine(d, n, seed=0, p_error=0.1)
         eng.reset()
         acts = torch.stack([torch.randint(0, 2, (n,)), torch.randint(0, d, (n,)), torch.randint(0, d, (n,)),
