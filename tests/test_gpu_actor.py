@@ -306,3 +306,19 @@ def test_cuda_graph_replay_equals_eager(pkg, d, n):
     pa, pb = a.perspective_views(), b.perspective_views()
     for x, y in zip(pa, pb):
         assert torch.equal(x, y)
+
+
+def test_multi_gpu_nccl(pkg):
+    """scripts/gpu_multi_check.py under torchrun on 2 GPUs: weight broadcast, sharded evaluate == single-GPU
+    evaluate, actor-step slices == one big batch, counters all-reduce to the big batch's.  Needs >= 2 GPUs."""
+    import os
+    import subprocess
+    import sys
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(root, "scripts", "gpu_multi_check.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    assert '"multi_gpu_check": "ok"' in res.stdout
