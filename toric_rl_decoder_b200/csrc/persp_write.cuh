@@ -73,6 +73,7 @@ struct PerspCfg {
   static constexpr bool kWide = (2 * D > 32);
   using TabT = typename std::conditional<kWide, unsigned long long, uint32_t>::type;
   static constexpr int kWarps = TC_WRITE_WARPS;
+  static constexpr int kEpb = 256 / (D <= 8 ? 8 : (D <= 16 ? 16 : 32));   // envs per CTA of the count kernels
   static constexpr int kPMax = 2 * D * D;
   static constexpr int kDD = D * D;
   static constexpr int kFields = (31 + D - 1) / D + 1;          // row fields overlapping one word
@@ -197,7 +198,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       pl = __ldg(syn + e * 2 * D + D + lane);
     }
     int64_t off = 0;
-    if (lane == 0) off = __ldg(block_off + e / epb) + (int64_t)__ldg(local_off + e);
+    if (lane == 0) off = __ldg(block_off + e / Cfg::kEpb) + (int64_t)__ldg(local_off + e);   // a shift
     uint32_t m0, m1;
     persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
     const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
@@ -424,7 +425,9 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     __syncwarp();
   }
   __syncwarp();
-  if (elect_one()) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  // the staging tiles must stay valid until the TMA engine has READ them; the global writes themselves complete
+  // by grid end like any other store (same as a CUTLASS TMA-store epilogue's tma_store_wait<0>)
+  if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
 }  // namespace tc

@@ -486,6 +486,7 @@ void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* p
 #ifndef TC_WRITE_SPLIT
 #define TC_WRITE_SPLIT 0          /* 0 = automatic */
 #endif
+  if (w.epb != Cfg::kEpb) return;             // the count kernels' CTA shape is baked into the writer
   int split = 1;
   if (!Cfg::kPlane) {
     if (TC_WRITE_SPLIT > 0) {
