@@ -279,8 +279,16 @@ def run_b200(a):
     # ---- e2e: reference-facing call with HOST buffers (actions in, step results out) ----------
     e2e = e2e_rows = None
     if not a.no_e2e:
-        e2e = run_e2e(a, eng, dev, dist, barrier, world, "u8")
-        e2e_rows = run_e2e(a, eng, dev, dist, barrier, world, "rows")
+        del eng
+        torch.cuda.empty_cache()
+
+        def make_engine():
+            e = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p, out_dtype=out_dtype)
+            e.ensure_capacity(e.worst_case_capacity())
+            return e
+        recorded = record_device_policy(a, make_engine, max(3, a.warmup) + a.steps)
+        e2e = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "u8")
+        e2e_rows = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "rows")
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -308,63 +316,86 @@ def run_b200(a):
         dist.destroy_process_group()
 
 
-def run_e2e(a, eng, dev, dist, barrier, world, states):
+def record_device_policy(a, make_engine, total_steps):
+    """The device's random-policy trajectory (the one `value` times), recorded once: actions (steps,n,4) int32 in
+    pinned host memory plus the running perspective total after every step."""
+    import torch
+    rec = make_engine()
+    rec.reset()
+    host = torch.empty((total_steps, a.envs, 4), dtype=torch.int32).pin_memory()
+    sum_p = []
+    for k in range(total_steps):
+        rec.actor_step()
+        host[k].copy_(rec.actions, non_blocking=True)
+        sum_p.append(rec.counters[5].clone())
+    torch.cuda.synchronize()
+    sum_p = [int(x.item()) for x in sum_p]
+    del rec
+    torch.cuda.empty_cache()
+    return host, sum_p
+
+
+def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states):
     """Same metric through the host-facing call (toric_rl_decoder_b200.HostActorPipeline): every step copies
     that step's actions (n,4) int32 from pinned host memory, runs the fused actor step, and reads rewards,
     terminals, perspective counts and the new states (uint8 n,2,d,d) back to pinned host memory.  Uploads
     and downloads run on their own streams with up to three steps in flight; every step's results are read on
     the host inside the timed region.
+    The host policy replays the actions the device's random policy chose on the same seed (recorded beforehand,
+    record_device_policy), so the envs walk exactly the trajectory `value` was timed on -- same resets, same
+    perspectives per env -- and the perspective totals are checked against the recording.
     The perspective tensor stays on the device, where the reference also puts it (`.to(device)`,
     src/numba/util_actor.py:39).  states="u8" (the `e2e` key) downloads the reference's one-byte-per-stabiliser
     array; states="rows" (`e2e_state_rows`) downloads np.packbits(states, axis=-1, bitorder="little") instead --
     at 8 ranks the box's aggregate device->host rate (~90 GB/s, profiles/r01_e2e_scale_probe.txt), not the
     GPUs, bounds the u8 form."""
-    import numpy as np
     import torch
     from toric_rl_decoder_b200 import HostActorPipeline, sharding
-    d, n = a.d, a.envs
-    rng = np.random.default_rng(a.seed + 17)
-    n_buf = 8
-    host_actions = []
-    for _ in range(n_buf):     # host policy: uniformly random qubit and Pauli (valid for any state)
-        arr = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)],
-                       axis=1).astype(np.int32)
-        host_actions.append(torch.from_numpy(arr).pin_memory())
+    n = a.envs
+    host_actions, rec_sum_p = recorded
+    warm = host_actions.shape[0] - a.steps
+    eng = make_engine()
+    eng.reset()
     depth = 3
     pipe = HostActorPipeline(eng, depth=depth, states=states)
     skey = "states" if states == "u8" else "state_rows"
     checksum = 0.0
 
-    def run(steps):
+    def run(k0, k1):
         nonlocal checksum
-        for k in range(steps):
+        for k in range(k0, k1):
             if pipe.submitted - pipe.collected >= depth:
                 res = pipe.collect()                    # the oldest step in flight is in host memory now
                 checksum += float(res["reward"][0]) + float(res[skey][0, 0, 0, 0])
-            pipe.submit(host_actions[k % n_buf], auto_reset=True)
+            pipe.submit(host_actions[k], auto_reset=True)
         while pipe.collected < pipe.submitted:
             res = pipe.collect()
             checksum += float(res["reward"][0])
 
-    run(max(3, a.warmup))
+    run(0, warm)
     barrier()
     c0 = eng.counters.clone()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
-    run(a.steps)
+    run(warm, warm + a.steps)
     ev1.record()
     barrier()
     ms = ev0.elapsed_time(ev1)
     ms = sharding.max_over_ranks(ms, dev)
     dc = eng.counters - c0
-    return {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
-            "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
-            "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
-            "call": "HostActorPipeline.submit(pinned host actions) / collect() -> host reward, terminal, counts, "
-                    "%s; uploads and downloads on their own streams, up to 3 steps in flight"
-                    % ("states uint8 (n,2,d,d)" if states == "u8" else
-                       "state_rows uint8 (n,2,d,ceil(d/8)) = packbits(states, little)"),
-            "policy": "host-supplied uniformly random qubit + Pauli"}
+    assert int(eng.counters[5].item()) == rec_sum_p[-1], "host-buffer run left the recorded trajectory"
+    out = {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
+           "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
+           "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
+           "call": "HostActorPipeline.submit(pinned host actions) / collect() -> host reward, terminal, counts, "
+                   "%s; uploads and downloads on their own streams, up to 3 steps in flight"
+                   % ("states uint8 (n,2,d,d)" if states == "u8" else
+                      "state_rows uint8 (n,2,d,ceil(d/8)) = packbits(states, little)"),
+           "policy": "host-supplied actions = the device random policy's choices on the same seed (recorded), "
+                     "i.e. the trajectory `value` is timed on"}
+    del pipe, eng
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():

@@ -61,7 +61,9 @@ __global__ void pack_state_kernel(const uint8_t* __restrict__ st, uint32_t* __re
 __global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t total) {
   const int64_t b0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (b0 >= total) return;
-  int64_t row = b0 / d;
+  int64_t row;
+  if (total <= 0x7fffffff) row = (int64_t)((uint32_t)b0 / (uint32_t)d);   // 32-bit divide: a 64-bit one is a subroutine
+  else row = b0 / d;
   int j = (int)(b0 - row * d);
   uint32_t w = syn[row];
   uint32_t out[2] = {0u, 0u};
