@@ -202,13 +202,15 @@ class ToricEngine:
                                            self.workspace.numel(), self.d, n, _stream()), "tc_persp_count")
 
     def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
-                   freeze_done=False, actions_buffer=None, results=None):
+                   freeze_done=False, actions_buffer=None, results=None, between=None):
         """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
         self.actions itself (e.g. filled by select_action) skips the copy; actions_buffer (device int32
         (n,4), 16-byte aligned) is read in place instead of self.actions.  freeze_done leaves envs whose
         syndrome is already trivial untouched (batched evaluation).  results = (reward f32 (n,), terminal u8
         (n,), counts i32 (n,)) device tensors to receive this step's results instead of self.reward /
-        self.terminal / self.counts (HostActorPipeline points them into its download block)."""
+        self.terminal / self.counts (HostActorPipeline points them into its download block).  between: a
+        callable run after the step / count kernels are enqueued and before the perspective writer is (the
+        step's results and new states are final at that point; HostActorPipeline records an event there)."""
         flags = (ACTOR_AUTO_RESET if auto_reset else 0) | (ACTOR_FREEZE_DONE if freeze_done else 0)
         reward, terminal, counts = results if results is not None else (self.reward, self.terminal, self.counts)
         act_buf = self.actions
@@ -225,13 +227,15 @@ class ToricEngine:
         self._last_syn = self.syn
         # `overflow` is sticky here (cleared by perspectives() / perspective_views()): no memset between the
         # writer of one step and the first kernel of the next, so the launches chain back to back
-        if self.out_dtype is not torch.float32:      # fused entry point is float32; same two halves otherwise
+        if self.out_dtype is not torch.float32 or between is not None:   # the fused entry point's two halves
             _lib.check(self.lib.tc_actor_pre(
                 _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
                 _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
                 _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
                 int(n_fixed), self.seed, self.env_base, _ptr(counts), _ptr(self.offsets), _ptr(self.workspace),
                 self.workspace.numel(), self.d, self.n, _stream()), "tc_actor_pre")
+            if between is not None:
+                between()
             self.persp_write()
             return
         _lib.check(self.lib.tc_actor_step(

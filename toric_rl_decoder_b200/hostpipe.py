@@ -5,8 +5,8 @@ new states back as host arrays (src/Actor_mp.py:116-125, src/EnvSet.py:38-47).  
 that contract on the GPU engine and overlaps the PCIe copies with the kernels:
 
     h2d stream:      actions(k+1)
-    compute stream:  actor_step(k) | snapshot(k) | actor_step(k+1) | snapshot(k+1) ...
-    d2h stream:                                  | results(k)                      | results(k+1)
+    compute stream:  step+count(k) | perspective writer(k)       | step+count(k+1) | writer(k+1) ...
+    d2h stream:                    | unpack(k) | results(k)                        | unpack(k+1) | results(k+1)
 
 (two copy streams: on a single one the upload of step k+1 would queue behind the download of step k, which
 waits for compute k, and nothing would overlap)
@@ -56,6 +56,7 @@ class HostActorPipeline:
                 "d_stage": torch.empty(self.nbytes, dtype=torch.uint8, device=dev),
                 "h_stage": torch.empty(self.nbytes, dtype=torch.uint8).pin_memory(),
                 "ev_actions": torch.cuda.Event(), "ev_compute": torch.cuda.Event(), "ev_result": torch.cuda.Event(),
+                "ev_unpacked": torch.cuda.Event(),
                 "busy": False,
             }
             hs = slot["h_stage"].numpy()
@@ -77,10 +78,16 @@ class HostActorPipeline:
             self.slots.append(slot)
         self.submitted = 0
         self.collected = 0
+        self._ev_unpacked = None
 
     def submit(self, actions_host, auto_reset=True):
         """Enqueue one step.  actions_host: pinned int32 tensor (n,4).  Never blocks the host unless the
-        ring is full (then the oldest result must be collected first)."""
+        ring is full (then the oldest result must be collected first).
+
+        The step's results (reward, terminal, counts, new states) are final once the step / count kernels have
+        run, i.e. BEFORE the perspective writer: an event is recorded there, and the state unpack kernel and the
+        download run on the d2h stream behind that event, overlapping the writer.  The next step's first kernel
+        waits for the unpack (it rewrites the syndromes the unpack reads)."""
         if self.submitted - self.collected >= self.depth:
             raise RuntimeError("pipeline full: collect() before submitting again")
         eng = self.eng
@@ -90,18 +97,23 @@ class HostActorPipeline:
             slot["d_actions"].copy_(actions_host, non_blocking=True)
             slot["ev_actions"].record(self.h2d_stream)
         compute.wait_event(slot["ev_actions"])
+        if self._ev_unpacked is not None:
+            compute.wait_event(self._ev_unpacked)         # the previous step's unpack has read eng.syn
         # the step writes reward / terminal / counts straight into the slot's download block
         eng.actor_step(auto_reset=auto_reset, actions_buffer=slot["d_actions"],
-                       results=(slot["d_reward"], slot["d_term"], slot["d_counts"]))
-        if self.states == "u8":
-            _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
-                                               compute.cuda_stream), "tc_unpack_state")
-        elif self.states == "rows":
-            _lib.check(eng.lib.tc_state_rows(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
-                                             compute.cuda_stream), "tc_state_rows")
-        slot["ev_compute"].record(compute)
+                       results=(slot["d_reward"], slot["d_term"], slot["d_counts"]),
+                       between=lambda: slot["ev_compute"].record(compute))
         with torch.cuda.stream(self.d2h_stream):
             self.d2h_stream.wait_event(slot["ev_compute"])
+            if self.states == "u8":
+                _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
+                                                   self.d2h_stream.cuda_stream), "tc_unpack_state")
+            elif self.states == "rows":
+                _lib.check(eng.lib.tc_state_rows(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
+                                                 self.d2h_stream.cuda_stream), "tc_state_rows")
+            if self.states is not None:
+                slot["ev_unpacked"].record(self.d2h_stream)
+                self._ev_unpacked = slot["ev_unpacked"]
             slot["h_stage"].copy_(slot["d_stage"], non_blocking=True)
             slot["ev_result"].record(self.d2h_stream)
         self.submitted += 1
