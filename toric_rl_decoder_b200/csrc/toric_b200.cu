@@ -461,7 +461,7 @@ inline Workspace carve(void* ws, int d, int64_t n) {
 
 // persistent grid: one CTA slot per (SM x resident CTAs), capped by the number of envs
 template <int D, typename OutT>
-void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* pos, int64_t* offsets,
+int launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* pos, int64_t* offsets,
                   int32_t* overflow, int64_t cap, int64_t n, uint32_t one16, cudaStream_t st) {
   using Cfg = PerspCfg<D>;
   constexpr int WPB = Cfg::kWarps;
@@ -488,7 +488,7 @@ void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* p
 #ifndef TC_WRITE_SPLIT
 #define TC_WRITE_SPLIT 0          /* 0 = automatic */
 #endif
-  if (w.epb != Cfg::kEpb) return;             // the count kernels' CTA shape is baked into the writer
+  if (w.epb != Cfg::kEpb) return -1;          // the count kernels' CTA shape is baked into the writer
   int split = 1;
   if (!Cfg::kPlane) {
     if (TC_WRITE_SPLIT > 0) {
@@ -505,13 +505,17 @@ void launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* p
   if (TC_WRITE_WAVES > 0 && grid > (unsigned)slots[dev] * TC_WRITE_WAVES) grid = (unsigned)slots[dev] * TC_WRITE_WAVES;
   launch_pdl(persp_write_kernel<D, OutT>, grid, WPB * 32, Cfg::kSmemBytes, st, syn, (const int32_t*)w.local_off,
              (const int64_t*)w.block_off, w.epb, out, pos, offsets, overflow, cap, n, one16, split);
+  return 0;
 }
 
 template <typename OutT>
 int write_dispatch(int d, const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* pos, int64_t* offsets,
                    int32_t* overflow, int64_t cap, int64_t n, uint32_t one16, cudaStream_t st) {
   switch (d) {
-#define TC_CASE(D) case D: launch_write<D, OutT>(syn, w, out, pos, offsets, overflow, cap, n, one16, st); break;
+#define TC_CASE(D) \
+  case D:          \
+    if (launch_write<D, OutT>(syn, w, out, pos, offsets, overflow, cap, n, one16, st) != 0) return -1; \
+    break;
     TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8) TC_CASE(9) TC_CASE(10)
     TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16) TC_CASE(17) TC_CASE(18)
     TC_CASE(19) TC_CASE(20) TC_CASE(21) TC_CASE(22) TC_CASE(23) TC_CASE(24) TC_CASE(25) TC_CASE(26)
