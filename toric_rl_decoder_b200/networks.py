@@ -22,6 +22,9 @@ CHANNELS = {
 class ConvDecoder(nn.Module):
     """Input (B,2,d,d) float32 perspectives -> (B,3) Q-values for X, Y, Z on the centred qubit."""
 
+    # rows are independent, so policy._forward may pad a small batch with zero rows (fewer distinct cuDNN shapes)
+    pad_small_batches = True
+
     def __init__(self, arch, system_size, number_of_actions=3, device=None):
         super().__init__()
         chans = CHANNELS[arch]

@@ -48,7 +48,7 @@ def _forward(model, persp, chunk=1 << 16):
         return torch.zeros((0, 3), dtype=torch.float32, device=persp.device)
     with torch.no_grad():
         n = persp.shape[0]
-        if n <= 4096 and n % 64:
+        if n <= 4096 and n % 64 and getattr(model, "pad_small_batches", False):
             # single-env / small-batch use: every step has a different number of perspectives, and cuDNN spends
             # milliseconds choosing kernels for each new batch size; 64 sizes instead of 4096
             padded = torch.zeros((n + 63) // 64 * 64, *persp.shape[1:], dtype=persp.dtype, device=persp.device)
