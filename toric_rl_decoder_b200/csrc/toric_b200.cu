@@ -56,30 +56,34 @@ __global__ void pack_state_kernel(const uint8_t* __restrict__ st, uint32_t* __re
   syn[t] = w;
 }
 
-// 8 output bytes per thread, written as one 8-byte store: byte b of the flat [n][2][d][d] array is bit b % d of
-// row word b / d
-__global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t total) {
-  const int64_t b0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+// 16 output bytes per thread, written as one 16-byte store: byte b of the flat [n][2][d][d] array is bit b % d of
+// row word b / d.  The (at most 6, d >= 3) row words a thread needs are all loaded before the first use.
+__global__ void unpack_state_kernel(const uint32_t* __restrict__ syn, uint8_t* __restrict__ st, int d, int64_t total,
+                                    int64_t n_rows) {
+  const int64_t b0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
   if (b0 >= total) return;
   int64_t row;
   if (total <= 0x7fffffff) row = (int64_t)((uint32_t)b0 / (uint32_t)d);   // 32-bit divide: a 64-bit one is a subroutine
   else row = b0 / d;
   int j = (int)(b0 - row * d);
-  uint32_t w = syn[row];
-  uint32_t out[2] = {0u, 0u};
+  uint32_t w[6];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    out[k >> 2] |= ((w >> j) & 1u) << (8 * (k & 3));
-    if (++j == d) {
-      j = 0;
-      ++row;
-      if (b0 + k + 1 < total) w = syn[row];
-    }
+  for (int k = 0; k < 6; ++k) w[k] = row + k < n_rows ? syn[row + k] : 0u;
+  // the thread's 16 stream bits (row fields of d bits, back to back), then 4 bits -> 4 bytes by a multiply
+  uint32_t bits = w[0] >> j;
+  int sh = d - j;
+#pragma unroll
+  for (int k = 1; k < 6; ++k) {
+    if (sh < 16) bits |= w[k] << sh;
+    sh += d;
   }
-  if (b0 + 8 <= total && (((uintptr_t)st) & 7) == 0) {
-    *reinterpret_cast<uint2*>(st + b0) = make_uint2(out[0], out[1]);
+  uint32_t out[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) out[q] = (((bits >> (4 * q)) & 15u) * 0x00204081u) & 0x01010101u;
+  if (b0 + 16 <= total && (((uintptr_t)st) & 15) == 0) {
+    *reinterpret_cast<uint4*>(st + b0) = make_uint4(out[0], out[1], out[2], out[3]);
   } else {
-    for (int k = 0; k < 8 && b0 + k < total; ++k) st[b0 + k] = (uint8_t)(out[k >> 2] >> (8 * (k & 3)));
+    for (int k = 0; k < 16 && b0 + k < total; ++k) st[b0 + k] = (uint8_t)(out[k >> 2] >> (8 * (k & 3)));
   }
 }
 
@@ -612,7 +616,8 @@ int tc_unpack_state(const uint32_t* syn, uint8_t* state01, int d, int64_t n, voi
   if (n == 0) return 0;            // an empty batch is legal (and has no buffers)
   if (!state01 || !syn) return -1;
   const int64_t total = n * 2 * d * d;
-  unpack_state_kernel<<<grid_for((total + 7) / 8, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, total);
+  unpack_state_kernel<<<grid_for((total + 15) / 16, 256), 256, 0, (cudaStream_t)stream>>>(syn, state01, d, total,
+                                                                                        n * 2 * d);
   return launch_status();
 }
 
