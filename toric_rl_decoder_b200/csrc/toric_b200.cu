@@ -353,8 +353,11 @@ struct ActorArgs {
   int flags, max_steps, mode, n_fixed, d;
 };
 
+#ifndef TC_ACTOR_MIN_CTAS
+#define TC_ACTOR_MIN_CTAS 5   /* 48 registers: 5 CTAs per SM, 2048 CTAs at 65536 envs = 2.8 waves instead of 3.5 */
+#endif
 template <int G>
-__global__ void __launch_bounds__(kThreads, 4) actor_step_kernel(const ActorArgs a) {
+__global__ void __launch_bounds__(kThreads, TC_ACTOR_MIN_CTAS) actor_step_kernel(const ActorArgs a) {
   __shared__ unsigned int s_ctr[kNumCounters];
   if (threadIdx.x < kNumCounters) s_ctr[threadIdx.x] = 0;
   __syncthreads();
