@@ -267,3 +267,20 @@ def test_empty_batch(pkg):
     eng2.perspectives()
     p2, _, c2, o2 = eng2.perspective_views()
     assert p2.shape[0] == 0 and (c2 == 0).all() and (o2 == 0).all()
+
+
+def test_engine_on_another_device_fails_loudly(pkg):
+    """The library launches on the current device: an engine living elsewhere raises instead of launching on the
+    wrong GPU, and works inside torch.cuda.device(...)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    with torch.cuda.device(1):
+        eng = pkg.ToricEngine(5, 16, device="cuda:1", seed=2)
+        eng.reset()
+        s1 = eng.get_state().cpu()
+    assert torch.cuda.current_device() == 0
+    with pytest.raises(RuntimeError):
+        eng.reset()
+    with torch.cuda.device(1):
+        eng.actor_step()
+        assert eng.get_state().device.index == 1 and s1.shape == (16, 2, 5, 5)

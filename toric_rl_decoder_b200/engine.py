@@ -40,7 +40,13 @@ def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
 
 
-def _stream():
+def _stream(device=None):
+    """torch's current stream as a cudaStream_t.  The library launches on the CURRENT device, so an engine that
+    lives on another device fails loudly here instead of launching on the wrong GPU (one process per GPU is the
+    intended layout; otherwise wrap the call in `with torch.cuda.device(engine.device):`)."""
+    if device is not None and device.index is not None and torch.cuda.current_device() != device.index:
+        raise RuntimeError("engine lives on %s but the current CUDA device is cuda:%d; wrap the call in "
+                           "torch.cuda.device(...)" % (device, torch.cuda.current_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -65,6 +71,8 @@ class ToricEngine:
             raise RuntimeError("ToricEngine needs a CUDA device; there is no CPU fallback")
         self.d, self.n = int(d), int(n)
         self.device = torch.device(device)
+        if self.device.type == "cuda" and self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         self.seed, self.env_base, self.max_steps = int(seed), int(env_base), int(max_steps)
         dev, n_, d_ = self.device, self.n, self.d
         z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=dev)  # noqa: E731
@@ -126,29 +134,29 @@ class ToricEngine:
         """Inject Pauli-code masks (n,2,d,d); the syndrome is recomputed and the sticky flag cleared, as
         the reference's scripts do by assigning env.qubit_matrix / env.state."""
         t = self._as_u8(codes, (self.n, 2, self.d, self.d))
-        _lib.check(self.lib.tc_pack_qubits(_ptr(t), _ptr(self.qubits), self.d, self.n, _stream()), "tc_pack_qubits")
+        _lib.check(self.lib.tc_pack_qubits(_ptr(t), _ptr(self.qubits), self.d, self.n, _stream(self.device)), "tc_pack_qubits")
         self.syndrome()
         self.gs.fill_(1)
 
     def get_qubits(self):
         out = torch.empty((self.n, 2, self.d, self.d), dtype=torch.uint8, device=self.device)
-        _lib.check(self.lib.tc_unpack_qubits(_ptr(self.qubits), _ptr(out), self.d, self.n, _stream()),
+        _lib.check(self.lib.tc_unpack_qubits(_ptr(self.qubits), _ptr(out), self.d, self.n, _stream(self.device)),
                    "tc_unpack_qubits")
         return out
 
     def set_state(self, state01):
         t = self._as_u8(state01, (self.n, 2, self.d, self.d))
-        _lib.check(self.lib.tc_pack_state(_ptr(t), _ptr(self.syn), self.d, self.n, _stream()), "tc_pack_state")
+        _lib.check(self.lib.tc_pack_state(_ptr(t), _ptr(self.syn), self.d, self.n, _stream(self.device)), "tc_pack_state")
 
     def get_state(self, syn=None):
         syn = self.syn if syn is None else syn
         out = torch.empty((syn.shape[0], 2, self.d, self.d), dtype=torch.uint8, device=self.device)
-        _lib.check(self.lib.tc_unpack_state(_ptr(syn), _ptr(out), self.d, syn.shape[0], _stream()), "tc_unpack_state")
+        _lib.check(self.lib.tc_unpack_state(_ptr(syn), _ptr(out), self.d, syn.shape[0], _stream(self.device)), "tc_unpack_state")
         return out
 
     # -- kernels ---------------------------------------------------------------------------------
     def syndrome(self):
-        _lib.check(self.lib.tc_syndrome(_ptr(self.qubits), _ptr(self.syn), self.d, self.n, _stream()), "tc_syndrome")
+        _lib.check(self.lib.tc_syndrome(_ptr(self.qubits), _ptr(self.syn), self.d, self.n, _stream(self.device)), "tc_syndrome")
 
     def reset(self, idx=None, mode=SAMPLE_DEPOLARIZING, n_fixed=0):
         """Resample the listed envs (all when idx is None) until each has a non-trivial syndrome."""
@@ -160,7 +168,7 @@ class ToricEngine:
             self.steps[idx_t] = 0
         _lib.check(self.lib.tc_reset(_ptr(self.qubits), _ptr(self.syn), _ptr(self.gs), _ptr(self.status),
                                      _ptr(self.p_thresh), _ptr(self.episode), _ptr(idx_t), n_idx, int(mode),
-                                     int(n_fixed), self.seed, self.env_base, self.d, _stream()), "tc_reset")
+                                     int(n_fixed), self.seed, self.env_base, self.d, _stream(self.device)), "tc_reset")
         if idx is None:
             self.steps.zero_()
 
@@ -171,12 +179,12 @@ class ToricEngine:
             raise ValueError("actions must have shape (%d, 4)" % self.n)
         self.actions.copy_(a.to(torch.int32), non_blocking=True)
         _lib.check(self.lib.tc_step(_ptr(self.qubits), _ptr(self.syn), _ptr(self.actions), _ptr(self.reward),
-                                    _ptr(self.terminal), _ptr(self.status), self.d, self.n, _stream()), "tc_step")
+                                    _ptr(self.terminal), _ptr(self.status), self.d, self.n, _stream(self.device)), "tc_step")
         self.steps += 1
         return self.reward, self.terminal
 
     def ground_state(self):
-        _lib.check(self.lib.tc_ground_state(_ptr(self.qubits), _ptr(self.gs), self.d, self.n, _stream()),
+        _lib.check(self.lib.tc_ground_state(_ptr(self.qubits), _ptr(self.gs), self.d, self.n, _stream(self.device)),
                    "tc_ground_state")
         return self.gs
 
@@ -191,7 +199,7 @@ class ToricEngine:
         self.overflow.zero_()
         _lib.check(self.lib.tc_perspectives_as(_ptr(syn), _ptr(self.out), OUT_DTYPES[self.out_dtype], _ptr(self.pos),
                                                _ptr(self.counts), _ptr(self.offsets), _ptr(self.overflow), self.cap,
-                                               _ptr(self.workspace), self.workspace.numel(), self.d, n, _stream()),
+                                               _ptr(self.workspace), self.workspace.numel(), self.d, n, _stream(self.device)),
                    "tc_perspectives_as")
 
     def perspectives_count(self, syn=None, n=None):
@@ -199,7 +207,7 @@ class ToricEngine:
         syn = self.syn if syn is None else syn
         n = syn.shape[0] if n is None else n
         _lib.check(self.lib.tc_persp_count(_ptr(syn), _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace),
-                                           self.workspace.numel(), self.d, n, _stream()), "tc_persp_count")
+                                           self.workspace.numel(), self.d, n, _stream(self.device)), "tc_persp_count")
 
     def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
                    freeze_done=False, actions_buffer=None, results=None, between=None):
@@ -233,7 +241,7 @@ class ToricEngine:
                 _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
                 _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
                 int(n_fixed), self.seed, self.env_base, _ptr(counts), _ptr(self.offsets), _ptr(self.workspace),
-                self.workspace.numel(), self.d, self.n, _stream()), "tc_actor_pre")
+                self.workspace.numel(), self.d, self.n, _stream(self.device)), "tc_actor_pre")
             if between is not None:
                 between()
             self.persp_write()
@@ -244,7 +252,7 @@ class ToricEngine:
             _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
             int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(counts),
             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace), self.workspace.numel(),
-            self.d, self.n, _stream()), "tc_actor_step")
+            self.d, self.n, _stream(self.device)), "tc_actor_step")
 
     def capture_actor_steps(self, k=1, **kwargs):
         """Capture k fused actor steps (actor_step(**kwargs), device-drawn actions by default) into one CUDA
@@ -279,7 +287,7 @@ class ToricEngine:
             _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps), _ptr(self.episode),
             _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode), int(n_fixed), self.seed,
             self.env_base, _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace), self.workspace.numel(),
-            self.d, self.n, _stream()), "tc_actor_pre")
+            self.d, self.n, _stream(self.device)), "tc_actor_pre")
 
     def persp_write(self):
         """Second half: the streaming perspective write for the state left by actor_pre()."""
@@ -288,7 +296,7 @@ class ToricEngine:
         _lib.check(self.lib.tc_persp_write_as(_ptr(self.syn), _ptr(self.out), OUT_DTYPES[self.out_dtype],
                                               _ptr(self.pos), _ptr(self.offsets), _ptr(self.overflow), self.cap,
                                               _ptr(self.workspace), self.workspace.numel(), self.d, self.n,
-                                              _stream()), "tc_persp_write_as")
+                                              _stream(self.device)), "tc_persp_write_as")
 
     # -- results ---------------------------------------------------------------------------------
     def total_perspectives(self, n=None):
