@@ -41,22 +41,27 @@ def c1(scale):
     d = 5
     model = networks.load_state(networks.NN_11(d, 3), os.path.join(GOLD, "Size_5_NN_11_state.pt"), device="cuda")
     cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
-    # single env, the reference's own use (one episode at a time): 20 episodes one after the other, after a warm-up
-    for seed in range(3):
-        evaluation.evaluate(model, "toric-code-v0", cfg, d // 2, "cuda", [0.1], num_of_episodes=1, num_of_steps=75,
-                            seed=100 + seed, keep_failed=False)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    tot_steps, solved = 0.0, 0.0
-    for seed in range(20):
-        ec, gs, steps, mq, _ = evaluation.evaluate(model, "toric-code-v0", cfg, d // 2, "cuda", [0.1], num_of_episodes=1,
-                                                   num_of_steps=75, seed=seed, keep_failed=False)
-        tot_steps += float(steps[0])
-        solved += float(ec[0])
-    torch.cuda.synchronize()
-    wall = time.perf_counter() - t0
-    emit(config="c1 d=5 p=0.1 greedy NN_11 (fp32, TF32 off), single env, 20 episodes one at a time", episodes=20,
-         success=solved / 20, mean_steps=tot_steps / 20, env_steps_per_s=tot_steps / wall, ms_per_episode=1e3 * wall / 20)
+    # single env, the reference's own use (one episode at a time): episodes one after the other, after a warm-up;
+    # eager loop, then one CUDA graph per decoding step (evaluation.GraphedGreedyDecoder, the default)
+    for use_graph, episodes in ((False, 20), (True, 200)):
+        for seed in range(3):
+            evaluation.evaluate(model, "toric-code-v0", cfg, d // 2, "cuda", [0.1], num_of_episodes=1, num_of_steps=75,
+                                seed=100 + seed, keep_failed=False, use_graph=use_graph)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        tot_steps, solved = 0.0, 0.0
+        for seed in range(episodes):
+            ec, gs, steps, mq, _ = evaluation.evaluate(model, "toric-code-v0", cfg, d // 2, "cuda", [0.1],
+                                                       num_of_episodes=1, num_of_steps=75, seed=seed,
+                                                       keep_failed=False, use_graph=use_graph)
+            tot_steps += float(steps[0])
+            solved += float(ec[0])
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        emit(config="c1 d=5 p=0.1 greedy NN_11 (fp32, TF32 off), single env, episodes one at a time, %s"
+             % ("one CUDA graph per decoding step" if use_graph else "eager loop"), episodes=episodes,
+             success=solved / episodes, mean_steps=tot_steps / episodes, env_steps_per_s=tot_steps / wall,
+             ms_per_episode=1e3 * wall / episodes)
     for n in (int(4096 * scale),):
         evaluation.evaluate(model, "toric-code-v0", cfg, d // 2, "cuda", [0.1], num_of_episodes=min(n, 64),
                             num_of_steps=75, keep_failed=False)

@@ -114,6 +114,39 @@ def test_evaluate_mirror_small(pkg):
     assert abs(steps[0] - round(nsteps / n, 1)) <= 0.1 + 1e-9
 
 
+@pytest.mark.parametrize("d,n", ((5, 1), (7, 1), (5, 24)))
+def test_graphed_decoder_equals_eager(pkg, d, n):
+    """evaluate() on launch-bound small batches replays one CUDA graph per decoding step
+    (evaluation.GraphedGreedyDecoder); results must equal the eager loop's on the same seeded episodes.  The
+    decoder (engine + graph) is built once per model and shape and reused across p_error values and seeds."""
+    from toric_rl_decoder_b200 import evaluation
+    model = load_model(d)
+    cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
+    ps = [0.1, 0.05]
+    flipped = 0
+    seeds = 6 if n == 1 else 2
+    for seed in range(seeds):
+        a = evaluation.evaluate(model, 'toric-code-v0', cfg, d // 2, 'cuda', ps, num_of_episodes=n, num_of_steps=75,
+                                seed=seed, use_graph=False)
+        b = evaluation.evaluate(model, 'toric-code-v0', cfg, d // 2, 'cuda', ps, num_of_episodes=n, num_of_steps=75,
+                                seed=seed, use_graph=True)
+        same = all((x == y).all() for x, y in zip(a[:3], b[:3])) and len(a[4]) == len(b[4]) and \
+            all((u == v).all() for u, v in zip(a[4], b[4]))
+        if d == 5 and n == 1:
+            # both paths run the network on the same 64-row batch (50 rows padded) -> bit-identical Q-values
+            assert same, (seed, a[:4], b[:4])
+        elif not same:
+            # other shapes: the eager loop pads sumP to a multiple of 64, the graph runs all `cap` rows; cuDNN may
+            # pick different kernels per batch size (Q differs in the last bits), so a near-tie may flip
+            flipped += 1
+            continue
+        assert np.allclose(a[3], b[3], rtol=1e-4), (a[3], b[3])
+    assert flipped <= 1, flipped
+    assert len(model._tc_graphed_decoders) == 1
+    # a batch past the launch-bound range keeps the eager loop
+    assert evaluation.graphed_decoder(model, d, evaluation.GRAPH_MAX_ROWS, 'cuda', 75) is None
+
+
 def test_prediction_smart_mirror_small(pkg, tmp_path):
     from toric_rl_decoder_b200 import evaluation
     d, n = 5, 256

@@ -61,6 +61,101 @@ def run_episodes(model, eng, num_of_steps, epsilon=0.0, fwd_chunk=1 << 15):
     return q_sum, q_cnt
 
 
+GRAPH_MAX_ROWS = 4096     # worst-case perspective rows (n * 2d^2) up to which a decoding step is launch-bound
+
+
+class GraphedGreedyDecoder:
+    """One whole greedy decoding step -- Q-network forward over the full fixed-capacity perspective buffer,
+    tc_select_action, Q bookkeeping, tc_actor_step(FREEZE_DONE) -- captured as ONE CUDA graph.
+
+    For the reference's own use of the path (src/evaluation.py:62-117: one episode at a time, BASELINE
+    configs[0]) a step is ~45 kernel launches for a few microseconds of work each (12 convolutions + padding +
+    activations of NN_11, plus the engine's kernels), and run_episodes() synchronises three times per step to
+    slice the network input to sumP.  Here the network always runs over all `cap` rows (rows past sumP are
+    never read: tc_select_action walks `offsets`), so every shape is static, the step is a single graph launch
+    and the only host read is a 4-byte "unsolved envs" counter.  Needs a network whose rows are independent
+    (`pad_small_batches`, true of the reference's conv decoders) and epsilon = 0 (the epsilon draw's Philox key
+    would be baked into the graph).  The engine is reused across run() calls; the caller reseeds it through
+    `reseed()` so that its sampler state equals a freshly built engine's."""
+
+    def __init__(self, model, d, n, device, num_of_steps):
+        self.model, self.n = model, int(n)
+        self.eng = eng = ToricEngine(d, n, device=device, max_steps=num_of_steps)
+        cap = (eng.worst_case_capacity() + 63) // 64 * 64
+        eng.ensure_capacity(cap)
+        eng.out.zero_()
+        dev = eng.device
+        self.q_sel = torch.zeros((self.n, 3), dtype=torch.float32, device=dev)
+        self.q_sum = torch.zeros((), dtype=torch.float64, device=dev)
+        self.q_cnt = torch.zeros((), dtype=torch.int64, device=dev)
+        self.unsolved = torch.zeros((), dtype=torch.int64, device=dev)
+        self.param_ptr = next(model.parameters()).data_ptr()
+        eng.perspectives()                         # trivial syndromes: every env is "solved", the body is a no-op
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):              # cuDNN picks its kernels outside the capture
+            for _ in range(3):
+                self._body()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+
+    def _body(self):
+        eng, n = self.eng, self.n
+        with torch.no_grad():
+            q = self.model(eng.out).float().contiguous()
+        select_action_device(q, eng.pos, eng.offsets, n, actions=eng.actions, q_sel=self.q_sel)
+        active = eng.counts > 0
+        chosen = self.q_sel.gather(1, (eng.actions[:, 3].long() - 1).clamp_(0, 2).unsqueeze(1)).squeeze(1)
+        self.q_sum += (chosen.double() * active).sum()
+        self.q_cnt += active.sum()
+        eng.actor_step(actions=eng.actions, auto_reset=False, freeze_done=True)
+        self.unsolved.copy_((eng.counts > 0).sum())
+
+    def reseed(self, seed, env_base, p_error):
+        """Put the engine in the state of ToricEngine(d, n, seed=seed, env_base=env_base, p_error=p_error)."""
+        eng = self.eng
+        eng.seed, eng.env_base = int(seed), int(env_base)
+        eng.set_p_error(p_error)
+        eng.episode.zero_()
+        eng.status.zero_()
+        eng.counters.zero_()
+        return eng
+
+    def run(self, num_of_steps):
+        """Same contract as run_episodes(model, eng, num_of_steps): the engine has been reset or injected."""
+        eng = self.eng
+        self.q_sum.zero_()
+        self.q_cnt.zero_()
+        eng.perspectives()
+        for _ in range(int(num_of_steps)):
+            self.graph.replay()
+            if int(self.unsolved.item()) == 0:
+                break
+        if int(eng.overflow.item()) != 0:
+            raise RuntimeError("perspective buffer overflow")
+        return self.q_sum.clone(), int(self.q_cnt.item())
+
+
+def graphed_decoder(model, d, n, device, num_of_steps, epsilon=0.0):
+    """The cached GraphedGreedyDecoder of `model` for this shape, or None when the step is not launch-bound
+    (more than GRAPH_MAX_ROWS rows), epsilon > 0, or the network does not declare independent rows."""
+    if epsilon != 0.0 or n * 2 * d * d > GRAPH_MAX_ROWS or not getattr(model, "pad_small_batches", False):
+        return None
+    dev = torch.device(device)
+    if dev.type == "cuda" and dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    key = (int(d), int(n), str(dev), int(num_of_steps), torch.backends.cudnn.allow_tf32,
+           torch.backends.cuda.matmul.allow_tf32, torch.is_autocast_enabled())
+    cache = model.__dict__.setdefault("_tc_graphed_decoders", {})
+    dec = cache.get(key)
+    if dec is None or dec.param_ptr != next(model.parameters()).data_ptr():
+        dec = cache[key] = GraphedGreedyDecoder(model, d, n, dev, num_of_steps)
+    return dec
+
+
 def _all_reduce_sums(vec):
     import torch.distributed as dist
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
@@ -76,7 +171,7 @@ def _rank_world():
 
 
 def _evaluate_one_p(model, d, device, p_error, num_of_episodes, epsilon, num_of_steps, mode, n_fixed, seed,
-                    chunk, keep_failed, flips_hist=None, episode_base=0):
+                    chunk, keep_failed, flips_hist=None, episode_base=0, use_graph=True):
     """All episodes of one p_error owned by this rank.  Returns the float64 sums
     [episodes, solved, ground_state_kept, steps, q_sum, q_count] (device) and the failed-syndrome list."""
     rank, world = _rank_world()
@@ -87,11 +182,15 @@ def _evaluate_one_p(model, d, device, p_error, num_of_episodes, epsilon, num_of_
     done = 0
     while done < count:
         n = min(chunk, count - done)
-        eng = ToricEngine(d, n, device=device, seed=seed, env_base=episode_base + base + done, p_error=p_error,
-                          max_steps=num_of_steps)
+        dec = graphed_decoder(model, d, n, device, num_of_steps, epsilon) if use_graph else None
+        if dec is not None:       # launch-bound small batch (the reference's one-episode-at-a-time use)
+            eng = dec.reseed(seed, episode_base + base + done, p_error)
+        else:
+            eng = ToricEngine(d, n, device=device, seed=seed, env_base=episode_base + base + done, p_error=p_error,
+                              max_steps=num_of_steps)
         eng.reset(mode=mode, n_fixed=n_fixed)
         init = eng.qubits.clone()
-        q_sum, q_cnt = run_episodes(model, eng, num_of_steps, epsilon)
+        q_sum, q_cnt = dec.run(num_of_steps) if dec is not None else run_episodes(model, eng, num_of_steps, epsilon)
         solved = (eng.syn.reshape(n, -1) != 0).sum(dim=1) == 0
         eng.gs.fill_(1)
         gs = eng.ground_state().bool()
@@ -120,7 +219,7 @@ def _evaluate_one_p(model, d, device, p_error, num_of_episodes, epsilon, num_of_
                 else:
                     failed.extend(list(qi))            # small_p_error_test.py:162
         done += n
-        del eng
+        eng = None
     return sums, failed
 
 
@@ -131,7 +230,7 @@ def _config_fields(env_config):
 
 def evaluate(model, env, env_config, grid_shift, device, prediction_list_p_error, num_of_episodes=1,
              num_actions=3, epsilon=0.0, num_of_steps=50, plot_one_episode=False, minimum_nbr_of_qubit_errors=0,
-             seed=0, chunk=None, keep_failed=True):
+             seed=0, chunk=None, keep_failed=True, use_graph=True):
     """evaluate (src/evaluation.py:10-124).  Returns (error_corrected_list, ground_state_list,
     average_number_of_steps_list, mean_q_list, failed_syndroms) like the reference.
     `env` (the gym id) and plot_one_episode are accepted for signature compatibility."""
@@ -151,7 +250,8 @@ def evaluate(model, env, env_config, grid_shift, device, prediction_list_p_error
     n_fixed = int(env_config.get("min_qbit_errors", 0))
     for i, p_error in enumerate(prediction_list_p_error):
         sums, failed = _evaluate_one_p(model, d, dev, float(p_error), int(num_of_episodes), epsilon, num_of_steps,
-                                       mode, n_fixed, seed, chunk, keep_failed, episode_base=i * int(num_of_episodes))
+                                       mode, n_fixed, seed, chunk, keep_failed, episode_base=i * int(num_of_episodes),
+                                       use_graph=use_graph)
         s = _all_reduce_sums(sums).cpu().numpy()
         n_ep = max(s[0], 1.0)
         error_corrected_list[i] = s[1] / n_ep
@@ -165,7 +265,7 @@ def evaluate(model, env, env_config, grid_shift, device, prediction_list_p_error
 def prediction_smart(model, env, env_config, grid_shift, device, prediction_list_p_error, num_of_episodes=1,
                      epsilon=0.0, num_of_steps=50, plot_one_episode=False, show_network=False, show_plot=False,
                      nbr_of_qubit_errors=0, print_Q_values=False, checkpoint=10000, seed=0, chunk=None,
-                     keep_failed=True):
+                     keep_failed=True, use_graph=True):
     """prediction_smart (results/small_p_error_test.py:56-191): episodes start from
     generateNPlusQRandomErrors(q = nbr_of_qubit_errors, p) (fixed q errors plus depolarizing errors on the
     other qubits, resampled while the syndrome is trivial), failures are binned by initial error weight and
@@ -188,7 +288,7 @@ def prediction_smart(model, env, env_config, grid_shift, device, prediction_list
         local = torch.zeros_like(hist)
         sums, failed = _evaluate_one_p(model, d, dev, float(p_error), int(num_of_episodes), epsilon, num_of_steps,
                                        mode, q, seed, chunk, keep_failed, flips_hist=local,
-                                       episode_base=i * int(num_of_episodes))
+                                       episode_base=i * int(num_of_episodes), use_graph=use_graph)
         s = _all_reduce_sums(sums).cpu().numpy()
         hist[1:] += _all_reduce_sums(local[1:].contiguous())
         n_ep = max(s[0], 1.0)
