@@ -42,6 +42,9 @@ def parse_args():
                     help="element type of the perspective tensor; float32 = the reference's (headline)")
     ap.add_argument("--sample-every", type=int, default=8,
                     help="time the writer kernel with CUDA events on every k-th step of the timed region")
+    ap.add_argument("--dump-launches", action="store_true",
+                    help="add the sum P and algorithmic bytes of every timed writer launch to the roofline object "
+                         "(to match an ncu capture of one launch of the same command, scripts/gpu_traffic.sh)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -250,6 +253,7 @@ def run_b200(a):
     ms = ev0.elapsed_time(ev1)
     write_ms = sum(evb[k].elapsed_time(evc[k]) for k in sampled) / len(sampled)
     sampled_sum_p = float(totals.sum().item()) / len(sampled)
+    per_launch_sum_p = [int(x) for x in totals.tolist()] if a.dump_launches else None
     ctr = eng.counters.clone()
     assert int(eng.overflow.item()) == 0
     ms = sharding.max_over_ranks(ms, dev)                  # time = max over ranks
@@ -269,10 +273,21 @@ def run_b200(a):
                 "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
                 "kernel_launches_timed": len(sampled),
                 "step_achieved": b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9}
+    if per_launch_sum_p is not None:
+        roofline["timed_launch_steps"] = sampled
+        roofline["timed_launch_sum_p"] = per_launch_sum_p
+        roofline["timed_launch_algorithmic_bytes"] = [write_kernel_bytes(d, n, sp, esz) for sp in per_launch_sum_p]
+    # dram read+write bytes of ONE writer launch from the committed `ncu --set full` capture, next to the
+    # algorithmic bytes of that same launch (the launch is chosen with sum P close to the bench average, so the
+    # figure is comparable with achieved x kernel_ms)
     tr = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tr) and a.out_dtype == "float32" and d == 7:
         try:
-            roofline["traffic"] = json.load(open(tr)).get("persp_write_bytes_per_launch")
+            tj = json.load(open(tr))
+            roofline["traffic"] = tj.get("persp_write_bytes_per_launch")
+            if tj.get("launch_algorithmic_bytes"):
+                roofline["traffic_launch_algorithmic_bytes"] = tj["launch_algorithmic_bytes"]
+                roofline["traffic_over_algorithmic"] = tj["persp_write_bytes_per_launch"] / tj["launch_algorithmic_bytes"]
         except Exception:
             pass
 
