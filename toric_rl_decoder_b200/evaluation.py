@@ -62,6 +62,7 @@ def run_episodes(model, eng, num_of_steps, epsilon=0.0, fwd_chunk=1 << 15):
 
 
 GRAPH_MAX_ROWS = 4096     # worst-case perspective rows (n * 2d^2) up to which a decoding step is launch-bound
+GRAPH_CACHE_SIZE = 8      # graphed decoders kept per model (one per lattice size / batch size / step cap)
 
 
 class GraphedGreedyDecoder:
@@ -152,6 +153,9 @@ def graphed_decoder(model, d, n, device, num_of_steps, epsilon=0.0):
     cache = model.__dict__.setdefault("_tc_graphed_decoders", {})
     dec = cache.get(key)
     if dec is None or dec.param_ptr != next(model.parameters()).data_ptr():
+        cache.pop(key, None)
+        while len(cache) >= GRAPH_CACHE_SIZE:      # each entry owns a graph memory pool: keep the most recent shapes
+            cache.pop(next(iter(cache)))
         dec = cache[key] = GraphedGreedyDecoder(model, d, n, dev, num_of_steps)
     return dec
 
