@@ -1,0 +1,70 @@
+#!/usr/bin/env python
+"""BASELINE.json configs[3] at the reference's own sample size: d=7 low-error sweep with the importance-sampled
+generator (results/small_p_error_test.py: q = d//2+1 forced errors + depolarizing p elsewhere), 2^21 syndromes per p
+(the reference ran 2*10^6 per p, results/small_p_error_test.py:13) for p = 5e-4 and 5e-3, 2^19 for p = 5e-2.
+Prints one JSON line per p with the failure counts next to both reference runs
+(data/evaluation_size_7_p_*.txt and results/evaluation_size_7.txt) and a two-sample z-score.
+
+  python scripts/c4_big.py [--scale 1.0]
+"""
+import argparse
+import json
+import math
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from toric_rl_decoder_b200 import evaluation, networks  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+# ground-state rate, P_l, mean steps: (data/evaluation_size_7_p_<p>.txt:2, results/evaluation_size_7.txt) -- 2e6 episodes each
+REF = {0.0005: ((0.999976, 3.877189105207568e-12, 4.0), 0.9999735),
+       0.005: ((0.9998975, 2.820680442648895e-08, 4.5), 0.9998785),
+       0.05: ((0.978193, 1.5482072989164814e-05, 8.6), 0.978138)}
+N_REF = 2000000
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--scale", type=float, default=1.0)
+    a = ap.parse_args()
+    d = 7
+    model = networks.load_state(networks.NN_11(d, 3), os.path.join(GOLD, "Size_7_NN_11_random_state.pt"), device="cuda")
+    model = networks.pad_channels(model, 8).to(memory_format=torch.channels_last)
+    torch.backends.cudnn.allow_tf32 = True
+    torch.backends.cuda.matmul.allow_tf32 = True
+    cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
+    for p, n in ((0.0005, 1 << 21), (0.005, 1 << 21), (0.05, 1 << 19)):
+        n = max(1024, int(n * a.scale))
+        t0 = time.perf_counter()
+        ec, gs, st, mq, hist, nfail, pl, _ = evaluation.prediction_smart(
+            model, "toric-code-v0", cfg, d // 2, "cuda", [p], num_of_episodes=n, num_of_steps=75,
+            nbr_of_qubit_errors=d // 2 + 1, seed=11, keep_failed=False)
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        (g_ref, pl_ref, st_ref), g_ref2 = REF[p]
+        f = 1.0 - float(gs[0])
+
+        def z(g_other):
+            fo = 1.0 - g_other
+            pooled = (f * n + fo * N_REF) / (n + N_REF)
+            return (f - fo) / math.sqrt(max(pooled * (1 - pooled), 1e-30) * (1.0 / n + 1.0 / N_REF))
+        print(json.dumps({
+            "config": "c4 d=7 importance-sampled sweep (NN_11 Size_7 converged weights, TF32 conv, padded channels)",
+            "p_error": p, "syndromes": n, "failures": int(round(f * n)), "failure_rate": f,
+            "failure_rate_reference_data": 1 - g_ref, "failure_rate_reference_results": 1 - g_ref2,
+            "z_vs_reference_data": z(g_ref), "z_vs_reference_results": z(g_ref2),
+            "z_between_the_two_reference_runs": ((1 - g_ref) - (1 - g_ref2)) / math.sqrt(
+                max(((1 - g_ref) + (1 - g_ref2)) / 2, 1e-30) * 2.0 / N_REF),
+            "solved": float(ec[0]), "P_l": float(pl[0]), "P_l_reference": pl_ref, "mean_steps": float(st[0]),
+            "mean_steps_reference": st_ref, "mean_q": float(mq[0]), "failures_by_initial_weight": {
+                str(int(k)): int(v) for k, v in zip(hist[0], hist[2]) if v > 0},
+            "syndromes_per_s": n / wall, "seconds": wall}), flush=True)
+
+
+if __name__ == "__main__":
+    main()

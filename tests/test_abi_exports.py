@@ -62,3 +62,16 @@ def test_product_does_not_import_oracle():
         if fn.endswith(".py"):
             src = open(os.path.join(pkg_dir, fn)).read()
             assert "oracle" not in src, fn
+
+
+def test_graphed_decoder_gating_without_gpu():
+    """evaluation.graphed_decoder only takes launch-bound, greedy, row-independent cases; everything else keeps
+    the eager loop (decided before any CUDA work, so checkable here)."""
+    from toric_rl_decoder_b200 import evaluation, networks
+    model = networks.NN_11(5, 3)
+    rows = evaluation.GRAPH_MAX_ROWS
+    assert evaluation.graphed_decoder(model, 5, rows // 50 + 1, "cuda", 75) is None          # not launch-bound
+    assert evaluation.graphed_decoder(model, 5, 1, "cuda", 75, epsilon=0.1) is None          # epsilon draw needs the seed
+    model.pad_small_batches = False
+    assert evaluation.graphed_decoder(model, 5, 1, "cuda", 75) is None                       # rows not declared independent
+    assert "_tc_graphed_decoders" not in model.__dict__
