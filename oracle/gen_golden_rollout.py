@@ -106,5 +106,20 @@ def main():
     np.savez_compressed(os.path.join(OUT, "golden_rollout_d7.npz"), **rollouts(ref, m7, 7, 0.1, 12, seed=7))
 
 
+def export_converged_d5():
+    """tests/golden/Size_5_NN_11_converged_state.pt: copy of the state_dict
+    network/converged/Size_5_NN_11_17_Mar_2020_22_33_59.pt, the network behind results/evaluation_size_5.txt
+    (results/small_p_error_test.py:12) -- used by scripts/c4_big.py --d 5 for the statistical check on a second
+    lattice size.  Does not touch the rollout fixtures."""
+    import torch
+    sd = torch.load(ref_loader.REF_ROOT + "/network/converged/Size_5_NN_11_17_Mar_2020_22_33_59.pt",
+                    map_location="cpu", weights_only=True)
+    torch.save({k: v.detach().float().clone() for k, v in sd.items()},
+               os.path.join(OUT, "Size_5_NN_11_converged_state.pt"))
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "converged5":
+        export_converged_d5()
+    else:
+        main()
