@@ -74,4 +74,4 @@ def test_graphed_decoder_gating_without_gpu():
     assert evaluation.graphed_decoder(model, 5, 1, "cuda", 75, epsilon=0.1) is None          # epsilon draw needs the seed
     model.pad_small_batches = False
     assert evaluation.graphed_decoder(model, 5, 1, "cuda", 75) is None                       # rows not declared independent
-    assert "_tc_graphed_decoders" not in model.__dict__
+    assert evaluation.decoders_of(model) == {}

@@ -142,7 +142,9 @@ def test_graphed_decoder_equals_eager(pkg, d, n):
             continue
         assert np.allclose(a[3], b[3], rtol=1e-4), (a[3], b[3])
     assert flipped <= 1, flipped
-    assert len(model._tc_graphed_decoders) == 1
+    assert len(evaluation.decoders_of(model)) == 1
+    import copy
+    copy.deepcopy(model)                                # the cache lives outside the module: still copyable
     # a batch past the launch-bound range keeps the eager loop
     assert evaluation.graphed_decoder(model, d, evaluation.GRAPH_MAX_ROWS, 'cuda', 75) is None
 

@@ -10,6 +10,7 @@ so with torch.distributed initialised the episode range is sharded over the rank
 all-reduced.
 """
 import math
+import weakref
 
 import numpy as np
 import torch
@@ -80,7 +81,8 @@ class GraphedGreedyDecoder:
     `reseed()` so that its sampler state equals a freshly built engine's."""
 
     def __init__(self, model, d, n, device, num_of_steps):
-        self.model, self.n = model, int(n)
+        self.n = int(n)
+        self._model = model                        # only until the capture below: the graph holds the kernels
         self.eng = eng = ToricEngine(d, n, device=device, max_steps=num_of_steps)
         cap = (eng.worst_case_capacity() + 63) // 64 * 64
         eng.ensure_capacity(cap)
@@ -102,11 +104,12 @@ class GraphedGreedyDecoder:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self._body()
+        self._model = None                         # no strong reference back to the cache key (see _DECODERS)
 
     def _body(self):
         eng, n = self.eng, self.n
         with torch.no_grad():
-            q = self.model(eng.out).float().contiguous()
+            q = self._model(eng.out).float().contiguous()
         select_action_device(q, eng.pos, eng.offsets, n, actions=eng.actions, q_sel=self.q_sel)
         active = eng.counts > 0
         chosen = self.q_sel.gather(1, (eng.actions[:, 3].long() - 1).clamp_(0, 2).unsqueeze(1)).squeeze(1)
@@ -140,6 +143,16 @@ class GraphedGreedyDecoder:
         return self.q_sum.clone(), int(self.q_cnt.item())
 
 
+# model -> {shape key: GraphedGreedyDecoder}.  Kept outside the module object (copy.deepcopy(model) and state_dict
+# stay untouched) and weakly keyed: the decoders go when the network does.
+_DECODERS = weakref.WeakKeyDictionary()
+
+
+def decoders_of(model):
+    """The graphed decoders currently cached for `model` ({shape key: GraphedGreedyDecoder})."""
+    return dict(_DECODERS.get(model, {}))
+
+
 def graphed_decoder(model, d, n, device, num_of_steps, epsilon=0.0):
     """The cached GraphedGreedyDecoder of `model` for this shape, or None when the step is not launch-bound
     (more than GRAPH_MAX_ROWS rows), epsilon > 0, or the network does not declare independent rows."""
@@ -150,7 +163,7 @@ def graphed_decoder(model, d, n, device, num_of_steps, epsilon=0.0):
         dev = torch.device("cuda", torch.cuda.current_device())
     key = (int(d), int(n), str(dev), int(num_of_steps), torch.backends.cudnn.allow_tf32,
            torch.backends.cuda.matmul.allow_tf32, torch.is_autocast_enabled())
-    cache = model.__dict__.setdefault("_tc_graphed_decoders", {})
+    cache = _DECODERS.setdefault(model, {})
     dec = cache.get(key)
     if dec is None or dec.param_ptr != next(model.parameters()).data_ptr():
         cache.pop(key, None)
