@@ -75,3 +75,20 @@ def test_graphed_decoder_gating_without_gpu():
     model.pad_small_batches = False
     assert evaluation.graphed_decoder(model, 5, 1, "cuda", 75) is None                       # rows not declared independent
     assert evaluation.decoders_of(model) == {}
+
+
+def test_empty_batches_and_bad_sizes_without_gpu(lib_path):
+    """n = 0 is legal through the state entry points and returns before any pointer is looked at or any kernel is
+    launched (so it is checkable without a device); negative n and out-of-range d are -1 whatever the pointers."""
+    from toric_rl_decoder_b200 import _lib
+    lib = _lib.load()
+    assert lib.tc_syndrome(None, None, 7, 0, None) == 0
+    assert lib.tc_step(None, None, None, None, None, None, 7, 0, None) == 0
+    assert lib.tc_ground_state(None, None, 7, 0, None) == 0
+    assert lib.tc_pack_qubits(None, None, 7, 0, None) == 0 and lib.tc_unpack_qubits(None, None, 7, 0, None) == 0
+    assert lib.tc_pack_state(None, None, 7, 0, None) == 0 and lib.tc_unpack_state(None, None, 7, 0, None) == 0
+    assert lib.tc_state_rows(None, None, 7, 0, None) == 0
+    for d, n in ((7, -1), (2, 0), (33, 0), (0, 5)):
+        assert lib.tc_syndrome(None, None, d, n, None) == -1
+        assert lib.tc_ground_state(None, None, d, n, None) == -1
+        assert lib.tc_state_rows(None, None, d, n, None) == -1
