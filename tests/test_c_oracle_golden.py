@@ -90,3 +90,30 @@ def test_random_action_is_from_list():
             assert any((a[:3] == p).all() for p in pos) and 1 <= a[3] <= 3
         else:
             assert tuple(a[:3]) == (0, 0, 0)
+
+
+@pytest.mark.parametrize("d", (8, 10, 11, 13, 16, 20, 31, 32))
+def test_c_oracle_equals_numpy_oracle_at_sizes_without_fixtures(d):
+    """The two restatements are independent (numpy rolls vs explicit C index loops); at lattice sizes the golden
+    fixtures do not cover they must still agree with each other -- syndrome, step, reward, terminal, logical flag
+    and perspectives, including the largest size the engine accepts."""
+    rng = np.random.default_rng(500 + d)
+    for trial in range(3):
+        p = (0.01, 0.08, 0.3)[trial]
+        q = ((rng.random((2, d, d)) < p) * rng.integers(1, 4, (2, d, d))).astype(np.int64)
+        s = O.syndrome(q)
+        assert (C.syndrome(q) == s).all()
+        assert C.ground_state(q) == O.ground_state(q)
+        views, pos = O.perspectives(s)
+        cv, cp = C.perspectives(s)
+        assert (cv == views).all() and (cp == pos).all()
+        qc, sc = q.astype(np.uint8), s.astype(np.uint8)
+        qo, so = q, s
+        for t in range(6):
+            a = [int(rng.integers(2)), int(rng.integers(d)), int(rng.integers(d)), int(rng.integers(1, 4))]
+            if t % 2 == 0:
+                a[1], a[2] = (0, d - 1)[int(rng.integers(2))], (0, d - 1)[int(rng.integers(2))]
+            qo, so2, r, term = O.step(qo, so, a)
+            rc, tc = C.step(qc, sc, a)
+            assert (qc == qo).all() and (sc == so2).all() and rc == r and tc == term
+            so = so2
