@@ -101,6 +101,49 @@ def test_envset_mirror_golden(pkg):
     assert (persp.cpu().numpy() == g["views"].astype(np.float32)).all()
 
 
+def test_envset_envs_views(pkg):
+    """EnvSet.envs[i] (src/EnvSet.py:14-16): per-env ToricCode surface on one row of the batch; the other envs of
+    the batch are not touched by anything done through a view."""
+    d, n = 5, 7
+    es = pkg.EnvSetB200({"size": d, "p_error": 0.1}, n, seed=5)
+    s0 = es.resetAll()
+    assert len(es.envs) == n and len(es.envs[1:3]) == 2 and es.envs[-1]._i == n - 1
+    with pytest.raises(IndexError):
+        es.envs[n]
+    q_all = es.engine.get_qubits().cpu().numpy().astype(np.int64)
+    for i, env in enumerate(es.envs):
+        assert (env.qubit_matrix == q_all[i]).all() and (env.state == s0[i]).all() and env.ground_state
+        assert abs(env.p_error - 0.1) < 1e-9 and env.system_size == d
+    # inject a mask into env 2, step it, evaluate its logical flag: oracle on that env, bit-identical rest
+    rng = np.random.default_rng(3)
+    q = (rng.random((2, d, d)) < 0.2) * rng.integers(1, 4, (2, d, d))
+    v = es.envs[2]
+    v.qubit_matrix = q
+    s = O.syndrome(q)
+    assert (v.qubit_matrix == q).all() and (v.state == s).all()
+    qo, so, gs = q.astype(np.int64), s, True
+    for t in range(6):
+        a = [int(rng.integers(2)), int(rng.integers(d)), int(rng.integers(d)), int(rng.integers(1, 4))]
+        st, r, term, info = v.step(a)
+        qo, so2, ro, to = O.step(qo, so, a)
+        assert (st == so2).all() and r == ro and term == to and info == {}
+        so = so2
+        gs = O.ground_state(qo, gs)
+        assert v.evalGroundState() == gs
+    now = es.engine.get_qubits().cpu().numpy().astype(np.int64)
+    keep = [i for i in range(n) if i != 2]
+    assert (now[keep] == q_all[keep]).all() and (now[2] == qo).all()
+    assert (es.engine.steps.cpu().numpy() == np.array([0, 0, 6, 0, 0, 0, 0])).all()
+    # state setter + reset of one env
+    v.state = np.zeros((2, d, d), dtype=int)
+    assert v.isTerminalState(v.state)
+    s3 = es.envs[3].reset(p_error=0.3)
+    assert s3.any() and (O.syndrome(es.envs[3].qubit_matrix) == s3).all() and abs(es.envs[3].p_error - 0.3) < 1e-9
+    now = es.engine.get_qubits().cpu().numpy().astype(np.int64)
+    keep = [i for i in range(n) if i not in (2, 3)]
+    assert (now[keep] == q_all[keep]).all()
+
+
 def test_single_env_api(pkg):
     """ToricCodeB200 mirrors gym_ToricCode's ToricCode, injected with a golden mask."""
     g = golden.per_d(5)

@@ -11,7 +11,8 @@ from collections import namedtuple
 import numpy as np
 import torch
 
-from .engine import (SAMPLE_DEPOLARIZING, SAMPLE_FIXED_WEIGHT, SAMPLE_ONE_DRAW, ToricEngine)
+from . import _lib
+from .engine import (SAMPLE_DEPOLARIZING, SAMPLE_FIXED_WEIGHT, SAMPLE_ONE_DRAW, ToricEngine, _ptr, _stream)
 
 _Box = namedtuple("Box", ["low", "high", "shape"])
 
@@ -139,6 +140,108 @@ class ToricCodeB200:
         pass
 
 
+class _EnvView:
+    """`EnvSet.envs[i]` (src/EnvSet.py:14-16: the reference keeps a list of deep-copied envs): env i of the batch
+    with ToricCode's attribute surface.  Every per-env buffer of the engine is env-major and contiguous, so row i is
+    itself a valid batch of one: the kernels run on that slice, the other envs are not touched."""
+
+    def __init__(self, envset, i):
+        self._es, self._i = envset, int(i)
+        self.system_size = envset.size
+
+    def _rows(self):
+        e, i = self._es.engine, self._i
+        return e, e.qubits[i:i + 1], e.syn[i:i + 1]
+
+    @property
+    def p_error(self):
+        th = int(self._es.engine.p_thresh[self._i].item()) & 0xffffffff
+        return th / 4294967296.0
+
+    @property
+    def qubit_matrix(self):
+        e, q, _ = self._rows()
+        out = torch.empty((1, 2, e.d, e.d), dtype=torch.uint8, device=e.device)
+        _lib.check(e.lib.tc_unpack_qubits(_ptr(q), _ptr(out), e.d, 1, _stream(e.device)), "tc_unpack_qubits")
+        return out[0].cpu().numpy().astype(np.int64)
+
+    @qubit_matrix.setter
+    def qubit_matrix(self, codes):
+        e, q, syn = self._rows()
+        t = e._as_u8(np.asarray(codes).astype(np.uint8)[None], (1, 2, e.d, e.d))
+        _lib.check(e.lib.tc_pack_qubits(_ptr(t), _ptr(q), e.d, 1, _stream(e.device)), "tc_pack_qubits")
+        _lib.check(e.lib.tc_syndrome(_ptr(q), _ptr(syn), e.d, 1, _stream(e.device)), "tc_syndrome")
+        e.gs[self._i] = 1
+
+    @property
+    def state(self):
+        e, _, syn = self._rows()
+        return e.get_state(syn)[0].cpu().numpy().astype(np.int64)
+
+    @state.setter
+    def state(self, s):
+        e, _, syn = self._rows()
+        t = e._as_u8((np.asarray(s) != 0).astype(np.uint8)[None], (1, 2, e.d, e.d))
+        _lib.check(e.lib.tc_pack_state(_ptr(t), _ptr(syn), e.d, 1, _stream(e.device)), "tc_pack_state")
+
+    @property
+    def ground_state(self):
+        return bool(self._es.engine.gs[self._i].item())
+
+    @ground_state.setter
+    def ground_state(self, v):
+        self._es.engine.gs[self._i] = 1 if v else 0
+
+    def reset(self, p_error=None):
+        """ToricCode.reset on this env only (what EnvSet.resetTerminalEnvs loops over, src/EnvSet.py:19-26)."""
+        if p_error is not None:
+            self._es.engine.set_p_error(float(p_error), idx=[self._i])
+        self._es._reset(np.array([self._i], dtype=np.int64))
+        return self.state
+
+    def step(self, action):
+        """ToricCode.step on this env only: (state, reward, terminal, {})."""
+        e, q, syn = self._rows()
+        i = self._i
+        a = torch.as_tensor(np.asarray(action, dtype=np.int32).reshape(1, 4)).to(e.device)
+        _lib.check(e.lib.tc_step(_ptr(q), _ptr(syn), _ptr(a), _ptr(e.reward[i:i + 1]), _ptr(e.terminal[i:i + 1]),
+                                 _ptr(e.status[i:i + 1]), e.d, 1, _stream(e.device)), "tc_step")
+        e.steps[i] += 1
+        return self.state, int(e.reward[i].item()), bool(e.terminal[i].item()), {}
+
+    def evalGroundState(self):
+        e, q, _ = self._rows()
+        _lib.check(e.lib.tc_ground_state(_ptr(q), _ptr(e.gs[self._i:self._i + 1]), e.d, 1, _stream(e.device)),
+                   "tc_ground_state")
+        return self.ground_state
+
+    def isTerminalState(self, state):
+        return bool(np.all(np.asarray(state) == 0))
+
+
+class _EnvList:
+    """The `envs` list of the reference's EnvSet as a lazy sequence (a batch may hold millions of envs)."""
+
+    def __init__(self, envset):
+        self._es = envset
+
+    def __len__(self):
+        return self._es.no_envs
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [_EnvView(self._es, k) for k in range(*i.indices(len(self)))]
+        i = int(i)
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError("env index out of range")
+        return _EnvView(self._es, i)
+
+    def __iter__(self):
+        return (_EnvView(self._es, k) for k in range(len(self)))
+
+
 class EnvSetB200:
     """EnvSet (src/EnvSet.py:4-51) over one engine batch.
 
@@ -156,6 +259,7 @@ class EnvSetB200:
         self.min_qbit_errors = int(min_err)
         self.numpy_compat = numpy_compat
         self.engine = ToricEngine(size, self.no_envs, device=device, seed=seed, env_base=env_base, p_error=p)
+        self.envs = _EnvList(self)
         self.states = self._states()
 
     def _states(self):
