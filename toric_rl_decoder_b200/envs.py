@@ -133,6 +133,12 @@ class ToricCodeB200:
         matrix[:, :, :] = eng.get_qubits()[0].cpu().numpy()
         return matrix
 
+    def plotToricCode(self, state, title):
+        """ToricCode.plotToricCode (ToricCode.py:220-286) draws the lattice with matplotlib and saves a PDF: no
+        graphics stack -- unavailable on this box.  Accepted and ignored, so that the reference's callers
+        (src/evaluation.py:72,103 with plot_one_episode=True, results/start_from_state.py:40,58) keep running."""
+        return None
+
     def render(self, mode="human"):
         pass
 
