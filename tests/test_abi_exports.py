@@ -92,3 +92,17 @@ def test_empty_batches_and_bad_sizes_without_gpu(lib_path):
         assert lib.tc_syndrome(None, None, d, n, None) == -1
         assert lib.tc_ground_state(None, None, d, n, None) == -1
         assert lib.tc_state_rows(None, None, d, n, None) == -1
+
+
+def test_reference_type_surface():
+    """The reference's record types on the path (src/util.py:9-15, src/Actor_mp.py:52-56) exist under the same names
+    with the same fields."""
+    import numpy as np
+    import toric_rl_decoder_b200 as pkg
+    assert pkg.Action._fields == ("position", "action")
+    assert pkg.Perspective._fields == ("perspective", "position")
+    assert pkg.Transition._fields == ("state", "action", "reward", "next_state", "terminal")
+    assert pkg.action_type.names == ("position", "op") and pkg.action_type["position"].shape == (3,)
+    t = pkg.transition_type(7)
+    assert t.names == ("perspective", "action", "reward", "next_perspective", "terminal")
+    assert t["perspective"].shape == (2, 7, 7) and t["terminal"] == np.dtype(bool) and t["reward"] == np.dtype(float)

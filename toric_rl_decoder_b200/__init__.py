@@ -8,8 +8,8 @@ from .buildlib import LIB_PATH, build  # noqa: F401
 from .engine import (ACTOR_AUTO_RESET, ACTOR_RANDOM_ACTIONS, SAMPLE_DEPOLARIZING, SAMPLE_FIXED_PLUS_P,  # noqa: F401
                      SAMPLE_FIXED_WEIGHT, ToricEngine, p_to_thresh)
 from .envs import EnvSetB200, ToricCodeB200, make  # noqa: F401
-from .perspectives import (Perspective, generatePerspective, generatePerspectiveBatch,  # noqa: F401
-                           generatePerspectiveOptimized)
+from .perspectives import (Action, Perspective, Transition, action_type, generatePerspective,  # noqa: F401
+                           generatePerspectiveBatch, generatePerspectiveOptimized, transition_type)
 from .policy import (computePrioritiesParallel, generateTransitionParallel, predictMaxOptimized,  # noqa: F401
                      rotate_state, selectAction, selectActionBatch, select_action_device, shift_state,
                      transitions_device)

@@ -13,6 +13,16 @@ import torch
 from .engine import ToricEngine
 
 Perspective = namedtuple("Perspective", ["perspective", "position"])   # src/util.py:12
+Action = namedtuple("Action", ["position", "action"])                  # src/util.py:9
+Transition = namedtuple("Transition", ["state", "action", "reward", "next_state", "terminal"])   # src/util.py:14-15
+action_type = np.dtype([("position", (int, 3)), ("op", int)])          # src/util.py:10 (np.int is gone in numpy 2)
+
+
+def transition_type(d):
+    """The structured dtype the reference's actor builds for its transition records (src/Actor_mp.py:52-56):
+    what generateTransitionParallel(..., trans_type=...) fills."""
+    return np.dtype([("perspective", (int, (2, d, d))), ("action", action_type), ("reward", float),
+                     ("next_perspective", (int, (2, d, d))), ("terminal", bool)])
 
 _engines = {}
 
