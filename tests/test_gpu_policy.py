@@ -206,3 +206,36 @@ def test_make_mirrors_gym_make(pkg):
     assert s.shape == (2, 5, 5) and s.any()
     with pytest.raises(ValueError):
         pkg.make("cartpole")
+
+
+@pytest.mark.parametrize("d", (5, 7))
+def test_single_env_and_parallel_spellings(pkg, pol, d):
+    """src/util_actor.py's other spellings of the same operations -- selectActionParallel (:132-175),
+    generatePerspectiveParallel (:178-186), generateTransition (:67-103), computePriorities (:105-124) -- against the
+    reference-made fixtures and the numpy oracle."""
+    states = pol["sel_states%d" % d]
+    q = torch.from_numpy(pol["sel_q%d" % d]).cuda()
+    actions, q_v = pkg.selectActionParallel(3, 0.0, d // 2, d, states, TableModel(q), "cuda")
+    assert (actions == pol["sel_actions%d" % d]).all() and (q_v == pol["sel_qv%d" % d]).all()
+    per, pos = pkg.generatePerspectiveParallel(d // 2, d, states[:6])
+    for e in range(6):
+        ov, op_ = O.perspectives(states[e])
+        assert len(per[e]) == len(ov) == len(pos[e])
+        assert all((a == b).all() for a, b in zip(per[e], ov)) and [tuple(x) for x in op_] == pos[e]
+    st, ns, act = pol["tr_state%d" % d], pol["tr_next%d" % d], pol["tr_action%d" % d]
+    trans, qs, qns = [], [], []
+    rng = np.random.default_rng(d)
+    for k in range(8):
+        t = pkg.generateTransition(act[k], float(pol["tr_reward%d" % d][k]), d // 2, st[k], ns[k],
+                                   bool(pol["tr_terminal%d" % d][k]))
+        assert isinstance(t, pkg.Transition) and isinstance(t.action, pkg.Action)
+        assert (t.state == pol["tr_out_prev%d" % d][k]).all() and (t.next_state == pol["tr_out_next%d" % d][k]).all()
+        assert tuple(t.action.position) == tuple(int(x) for x in pol["tr_out_pos%d" % d][k])
+        assert t.action.action == int(pol["tr_out_op%d" % d][k]) and t.reward == float(pol["tr_reward%d" % d][k])
+        trans.append(t)
+        qs.append(rng.normal(size=3).astype(np.float32) * 50)
+        qns.append(rng.normal(size=3).astype(np.float32) * 50)
+    pr = pkg.computePriorities(trans, qs, qns, 0.95)
+    A = np.array([list(t.action.position) + [t.action.action] for t in trans])
+    want = O.td_priorities(A, [t.reward for t in trans], np.array(qs), np.array(qns), 0.95)
+    assert pr.shape == (8,) and np.allclose(pr, want, rtol=1e-6, atol=1e-5)

@@ -10,7 +10,8 @@ from .engine import (ACTOR_AUTO_RESET, ACTOR_RANDOM_ACTIONS, SAMPLE_DEPOLARIZING
 from .envs import EnvSetB200, ToricCodeB200, make  # noqa: F401
 from .perspectives import (Action, Perspective, Transition, action_type, generatePerspective,  # noqa: F401
                            generatePerspectiveBatch, generatePerspectiveOptimized, transition_type)
-from .policy import (computePrioritiesParallel, generateTransitionParallel, predictMaxOptimized,  # noqa: F401
-                     rotate_state, selectAction, selectActionBatch, select_action_device, shift_state,
-                     transitions_device)
+from .policy import (calculateEpsilon, computePriorities, computePrioritiesParallel,  # noqa: F401
+                     generatePerspectiveParallel, generateTransition, generateTransitionParallel,
+                     predictMaxOptimized, rotate_state, selectAction, selectActionBatch, selectActionParallel,
+                     select_action_device, shift_state, transitions_device)
 from .hostpipe import HostActorPipeline  # noqa: F401

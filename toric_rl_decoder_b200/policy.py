@@ -195,3 +195,66 @@ def predictMaxOptimized(model, batch_state, grid_shift, system_size, device="cud
     _lib.check(lib.tc_segmented_max(_ptr(qq), _ptr(offsets), 0, _ptr(pad), _ptr(out), n, _stream()),
                "tc_segmented_max")
     return out.cpu()
+
+
+# ---- the single-env / "Parallel" spellings of src/util_actor.py, on the same device entry points ----------------
+
+def selectActionParallel(number_of_actions, epsilon, grid_shift, toric_size, state, model, device="cuda", seed=0,
+                         step=0):
+    """selectActionParallel (src/util_actor.py:132-175): the numpy-era spelling of selectActionBatch, same
+    arguments and returns ((N,4) actions, (N,3) Q-value rows of the chosen perspectives)."""
+    return selectActionBatch(number_of_actions, epsilon, grid_shift, toric_size, state, model, device=device,
+                             seed=seed, step=step)
+
+
+def generatePerspectiveParallel(grid_shift, toric_size, states, device="cuda"):
+    """generatePerspectiveParallel (src/util_actor.py:178-186): per env the list of (2,d,d) perspectives and the
+    list of (m,i,j) positions -- one batched tc_perspectives call, split per env on the host.  (The reference
+    wraps the two ragged lists in np.array, which numpy >= 1.24 refuses; lists are returned.)"""
+    from .perspectives import generatePerspectiveBatch
+    states = np.asarray(states)
+    persp, pos, counts, offsets = generatePerspectiveBatch(grid_shift, toric_size, states, device=device)
+    persp = persp.cpu().numpy().astype(states.dtype)
+    pos, off = pos.cpu().numpy(), offsets.cpu().numpy()
+    per_result = [[persp[k] for k in range(off[e], off[e + 1])] for e in range(len(states))]
+    pos_result = [[tuple(int(x) for x in pos[k]) for k in range(off[e], off[e + 1])] for e in range(len(states))]
+    return per_result, pos_result
+
+
+def generateTransition(action, reward, grid_shift, previous_state, state, terminal_state, device="cuda"):
+    """generateTransition (src/util_actor.py:67-103): one Transition(previous_perspective, Action((m,g,g), op),
+    reward, perspective, terminal) -- tc_transitions on a batch of one."""
+    from .perspectives import Action, Transition
+    state = np.asarray(state)
+    d = int(state.shape[-1])
+    if int(grid_shift) != d // 2:
+        raise ValueError("grid_shift must be toric_size // 2")
+    dev = torch.device(device)
+    act = torch.as_tensor(np.asarray(action, dtype=np.int64).reshape(1, 4)).to(device=dev, dtype=torch.int32)
+    op, on, ao = transitions_device(_pack(np.asarray(previous_state)[None], d, dev), _pack(state[None], d, dev),
+                                    act.contiguous(), d, out_dtype=torch.uint8)
+    a = ao[0].cpu().numpy()
+    return Transition(op[0].cpu().numpy().astype(state.dtype), Action((int(a[0]), int(a[1]), int(a[2])), int(a[3])),
+                      reward, on[0].cpu().numpy().astype(state.dtype), terminal_state)
+
+
+def computePriorities(local_buffer_trans, local_buffer_qs, local_buffer_qs_ns, discount_factor, device="cuda"):
+    """computePriorities (src/util_actor.py:105-124): |r + discount * max Q(s') - Q(s)[a]| for a list of Transition
+    records and their Q-value rows (tc_td_priorities; float32 arithmetic on the device)."""
+    n = len(local_buffer_trans)
+    A = np.zeros((1, n, 4), dtype=np.int64)
+    R = np.zeros((1, n), dtype=np.float64)
+    for i, t in enumerate(local_buffer_trans):
+        A[0, i, :3] = t.action.position
+        A[0, i, 3] = t.action.action
+        R[0, i] = t.reward
+    Q = np.asarray(local_buffer_qs, dtype=np.float32).reshape(1, n, 3)
+    Qn = np.asarray(local_buffer_qs_ns, dtype=np.float32).reshape(1, n, 3)
+    return computePrioritiesParallel(A, R, Q, Qn, discount_factor, device=device)[0].cpu().numpy()
+
+
+def calculateEpsilon(e, alpha, num):
+    """calculateEpsilon (src/util_actor.py:294-312): the per-actor exploration schedule e_i = e^(1 + i/(n-1) * alpha)
+    (host-side configuration arithmetic, one value per env; feeds tc_select_action's eps_thresh)."""
+    i = np.arange(int(num), dtype=np.float64)
+    return np.power(float(e), 1.0 + (i / max(1, int(num) - 1)) * float(alpha))
