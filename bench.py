@@ -36,7 +36,15 @@ def parse_args():
     ap.add_argument("--p", type=float, default=0.1)
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU (weak scaling)")
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--burnin", type=int, default=152,
+                    help="untimed, uncounted steps before --warmup (episode clocks are pre-staggered over "
+                         "[0, max_steps], so the timed region sees the stationary reset rate whatever --steps is)")
+    ap.add_argument("--no-stagger", action="store_true", help="keep every env's episode clock at 0 after reset")
     ap.add_argument("--cpu-envs", type=int, default=8192, help="envs in the bounded CPU sample")
+    ap.add_argument("--ref-step-seconds", type=float, default=0.25,
+                    help="--impl reference: CPU time one reference 'step' (a whole number of passes over the "
+                         "--cpu-envs sample) is calibrated to")
+    ap.add_argument("--ref-warm-seconds", type=float, default=2.0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--out-dtype", default="float32", choices=("float32", "bfloat16", "float16", "uint8"),
                     help="element type of the perspective tensor; float32 = the reference's (headline)")
@@ -144,15 +152,45 @@ def load_peaks():
 
 
 # ----------------------------------------------------------------------------------------------
-def cpu_arm(a, seconds, n_envs, threads=0):
-    """Time the oracle's C port of the same loop on the host cores (bounded sample)."""
+def _cpu_loop(a, n_envs, threads=0):
+    """The oracle's C port of the actor loop on the host cores, brought to the same stationary regime as the GPU
+    arm: episode clocks staggered over [0, max_steps], then burned in for one full episode length."""
+    import numpy as np
     from oracle import c_oracle as C
     loop = C.ActorLoop(a.d, n_envs, a.p, seed=a.seed, nthreads=threads)
-    loop.run(2)                                  # warm caches / page in the buffers
+    if not a.no_stagger:
+        base = 0
+        for sl in loop.slices:
+            sl.steps[:] = stagger_clocks(np.arange(base, base + sl.n), 75)
+            base += sl.n
+    return loop
+
+
+def stagger_clocks(env_ids, max_steps):
+    """Episode clock of env e at the start: a fixed pseudo-random value in [0, max_steps] (Knuth hash of the
+    global env id) -- in a long-running actor the envs are at independent points of their episodes."""
+    import numpy as np
+    h = (np.asarray(env_ids, dtype=np.uint64) * np.uint64(2654435761)) & np.uint64(0xffffffff)
+    return ((h * np.uint64(max_steps + 1)) >> np.uint64(32)).astype(np.int32)
+
+
+def _timed_cpu(loop, warm_seconds, seconds, min_passes=1):
+    """Warm for >= warm_seconds (thread pool, caches, pages, stationary regime), then time >= `seconds`."""
     t0 = time.perf_counter()
     loop.run(2)
-    per_step = max((time.perf_counter() - t0) / 2, 1e-6)
-    steps = max(3, int(seconds / per_step))
+    per_pass = max((time.perf_counter() - t0) / 2, 1e-6)
+    warm_passes = max(76, int(warm_seconds / per_pass))       # at least one full episode length
+    t0 = time.perf_counter()
+    loop.run(warm_passes)
+    per_pass = max((time.perf_counter() - t0) / warm_passes, 1e-6)
+    passes = max(min_passes, int(round(seconds / per_pass)))
+    return per_pass, passes
+
+
+def cpu_arm(a, seconds, n_envs, threads=0):
+    """Time the oracle's C port of the same loop on the host cores (bounded sample)."""
+    loop = _cpu_loop(a, n_envs, threads)
+    _, steps = _timed_cpu(loop, a.ref_warm_seconds, seconds, 3)
     c0 = loop.counters.copy()
     t0 = time.perf_counter()
     loop.run(steps)
@@ -160,39 +198,54 @@ def cpu_arm(a, seconds, n_envs, threads=0):
     c = loop.counters - c0
     return {"value": float(c[0]) / dt, "unit": UNIT, "cores": loop.nthreads, "kind": "port",
             "sample": "%d envs x %d steps, d=%d p=%g, C port of EnvSet.step + generatePerspectiveBatch + float32 "
-                      "concatenate (oracle/toric_oracle.c), one slice per thread, %.1f s; mean perspectives/env %.1f"
-                      % (n_envs, steps, a.d, a.p, dt, float(c[3]) / max(float(c[0]), 1.0)),
+                      "concatenate (oracle/toric_oracle.c), one slice per thread, %.1f s after a >= %.0f s warm-up in "
+                      "the stationary regime; mean perspectives/env %.1f, %d episodes ended"
+                      % (n_envs, steps, a.d, a.p, dt, a.ref_warm_seconds, float(c[3]) / max(float(c[0]), 1.0),
+                         int(c[1])),
             "seconds": dt, "steps": steps, "envs": n_envs}
 
 
 def run_reference(a):
     """--impl reference: the CPU arm.  The reference is pure Python/numba and cannot travel to the GPU box,
-    so this times the oracle's C port of the same loop (kind "port") with every host core; each step
-    advances a bounded sample of --cpu-envs environments once."""
+    so this times the oracle's C port of the same loop (kind "port") with every host core.  One reference
+    'step' = a bounded sample: `passes` passes over --cpu-envs environments (each pass advances every env of
+    the sample once), with `passes` calibrated so a step takes ~--ref-step-seconds; the worker threads are
+    created once and warmed for >= --ref-warm-seconds before the --warmup steps."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import c_oracle as C
-    loop = C.ActorLoop(a.d, a.cpu_envs, a.p, seed=a.seed, nthreads=0)
-    loop.run(max(a.warmup, 1))
+    loop = _cpu_loop(a, a.cpu_envs, 0)
+    per_pass, passes = _timed_cpu(loop, a.ref_warm_seconds, a.ref_step_seconds, 1)
+    for _ in range(max(a.warmup, 1)):
+        loop.run(passes)
     c0 = loop.counters.copy()
     t0 = time.perf_counter()
-    loop.run(a.steps)
+    for _ in range(a.steps):
+        loop.run(passes)
     dt = time.perf_counter() - t0
     c = loop.counters - c0
     value = float(c[0]) / dt
-    sample = ("%d envs x %d steps, d=%d p=%g, C port of EnvSet.step + generatePerspectiveBatch + float32 concatenate "
-              "(oracle/toric_oracle.c), one slice per thread; mean perspectives/env %.1f"
-              % (a.cpu_envs, a.steps, a.d, a.p, float(c[3]) / max(float(c[0]), 1.0)))
+    sample = ("%d reference steps x %d passes over %d envs (%.2f s per step, %.1f s timed), d=%d p=%g, C port of "
+              "EnvSet.step + generatePerspectiveBatch + float32 concatenate (oracle/toric_oracle.c), one slice per "
+              "thread, threads created once, >= %.0f s warm-up in the stationary regime; mean perspectives/env %.1f, "
+              "%d episodes ended"
+              % (a.steps, passes, a.cpu_envs, dt / a.steps, dt, a.d, a.p, a.ref_warm_seconds,
+                 float(c[3]) / max(float(c[0]), 1.0), int(c[1])))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
             "data": "synthetic", "config": {"workload": workload_name(a),
-                                            "note": "CPU arm: bounded sample of the same loop on the host cores"},
+                                            "note": "CPU arm: each step is a bounded sample of the same loop on the "
+                                                    "host cores (%d passes over %d envs)" % (passes, a.cpu_envs),
+                                            "passes_per_step": passes, "cpu_envs": a.cpu_envs},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": loop.nthreads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "gpu_launches": 0, "nonce": _nonce()}
     print(json.dumps(line), flush=True)
+
+
+def _nonce():
+    return "%s-%d" % (os.urandom(6).hex(), time.time_ns())
 
 
 # ----------------------------------------------------------------------------------------------
@@ -216,13 +269,14 @@ def run_b200(a):
     eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p,
                           out_dtype=out_dtype)                                              # envs shard by rank
     eng.ensure_capacity(eng.worst_case_capacity())
-    eng.reset()
+    prepare(a, eng)                             # reset, staggered episode clocks, untimed burn-in
 
     def barrier():
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
 
+    write_peak = measure_write_peak(dev)
     for _ in range(a.warmup):
         eng.actor_step()
     barrier()
@@ -261,6 +315,8 @@ def run_b200(a):
     c = {name: int(ctr[i].item()) for i, name in enumerate(pkg.engine.COUNTER_NAMES)}
     total_steps = c["env_steps"]
     assert total_steps == n * a.steps * world
+    if not a.no_stagger and a.steps >= 8:
+        assert c["episodes"] > 0, "the timed region saw no episode end: not the stationary regime"
     value = total_steps / (ms * 1e-3)
     sum_p_local = int(eng.counters[5].item())
     p_bar = sum_p_local / float(n * a.steps)
@@ -270,6 +326,9 @@ def run_b200(a):
     achieved = wbytes / (write_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": "persp_write_kernel<%d,%s>" % (d, a.out_dtype), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                # the kernel is a write-only stream and `peak` is a COPY (read+write) figure, so frac can exceed 1;
+                # write_peak is the write-only ceiling measured live (torch fill_ = a memset kernel, best of 5)
+                "write_peak": write_peak, "frac_of_write_peak": achieved / write_peak if write_peak else None,
                 "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
                 "kernel_launches_timed": len(sampled),
                 "step_achieved": b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9}
@@ -292,7 +351,7 @@ def run_b200(a):
             pass
 
     # ---- e2e: reference-facing call with HOST buffers (actions in, step results out) ----------
-    e2e = e2e_rows = None
+    e2e = e2e_open = e2e_u8 = None
     if not a.no_e2e:
         del eng
         torch.cuda.empty_cache()
@@ -302,8 +361,9 @@ def run_b200(a):
             e.ensure_capacity(e.worst_case_capacity())
             return e
         recorded = record_device_policy(a, make_engine, max(3, a.warmup) + a.steps)
-        e2e = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "u8")
-        e2e_rows = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "rows")
+        e2e = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 1)
+        e2e_open = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 3)
+        e2e_u8 = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "u8", 1)
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -319,16 +379,57 @@ def run_b200(a):
                 "config": {"workload": workload_name(a), "d": d, "p_error": a.p, "envs_per_gpu": n,
                            "global_envs": n * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
                            "mean_perspectives_per_env": p_bar, "out_dtype": a.out_dtype,
+                           "regime": ("stationary: episode clocks staggered over [0, %d], %d untimed burn-in steps "
+                                      "before the warm-up" % (eng.max_steps, a.burnin)) if not a.no_stagger else
+                                     "all envs start their first episode at the first warm-up step",
                            "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
                                  % (wbytes / 1e9),
                            "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_state_rows": e2e_rows,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_open_loop": e2e_open,
+                "e2e_u8_full": e2e_u8,
                 "gpu_launches": 3 * a.steps,
-                "clocks": clk.summary(),
+                "clocks": clk.summary(), "nonce": _nonce(),
                 "counters": {k: c[k] for k in ("episodes", "solved", "ground_kept", "timeouts", "perspectives")}}
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def prepare(a, eng):
+    """Fresh syndromes, then the stationary regime of a long-running actor: every env's episode clock starts at a
+    fixed pseudo-random point of [0, max_steps] (so time-outs, hence auto-resets, are spread evenly over the steps
+    instead of hitting all envs in the same step) and --burnin untimed steps of the device's random policy are
+    run and their counters dropped."""
+    import numpy as np
+    import torch
+    eng.reset()
+    if not a.no_stagger:
+        clocks = stagger_clocks(np.arange(eng.env_base, eng.env_base + eng.n), eng.max_steps)
+        eng.steps.copy_(torch.from_numpy(clocks))
+        for _ in range(a.burnin):
+            eng.actor_step()
+    eng.counters.zero_()
+
+
+def measure_write_peak(dev):
+    """Write-only HBM ceiling, measured live: torch fill_ (a plain memset kernel) over 2 GiB, best of 5."""
+    import torch
+    try:
+        buf = torch.empty(2 << 30, dtype=torch.uint8, device=dev)
+        best = None
+        for _ in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            buf.fill_(1)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1)
+            best = ms if best is None or ms < best else best
+        del buf
+        torch.cuda.empty_cache()
+        return (2 << 30) / (best * 1e-3) / 1e9
+    except Exception:
+        return None
 
 
 def record_device_policy(a, make_engine, total_steps):
@@ -336,7 +437,7 @@ def record_device_policy(a, make_engine, total_steps):
     pinned host memory plus the running perspective total after every step."""
     import torch
     rec = make_engine()
-    rec.reset()
+    prepare(a, rec)
     host = torch.empty((total_steps, a.envs, 4), dtype=torch.int32).pin_memory()
     sum_p = []
     for k in range(total_steps):
@@ -350,62 +451,88 @@ def record_device_policy(a, make_engine, total_steps):
     return host, sum_p
 
 
-def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states):
+def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
     """Same metric through the host-facing call (toric_rl_decoder_b200.HostActorPipeline): every step copies
     that step's actions (n,4) int32 from pinned host memory, runs the fused actor step, and reads rewards,
-    terminals, perspective counts and the new states (uint8 n,2,d,d) back to pinned host memory.  Uploads
-    and downloads run on their own streams with up to three steps in flight; every step's results are read on
-    the host inside the timed region.
+    terminals, perspective counts and the new states back to pinned host memory; every step's results are read
+    on the host inside the timed region (reward[0], the whole counts vector -- summed and checked against the
+    recorded trajectory -- and env 0's state through the `states` view).
+
+    depth=1 is the CLOSED loop of the reference's EnvSet.step contract (src/Actor_mp.py:116-125): the action of
+    step k+1 is submitted only after step k's results have been collected and read on the host.  The step's
+    results are final before the perspective writer runs, so their download (and the host's turn-around) overlaps
+    the writer of the same step.  depth=3 (`e2e_open_loop`) keeps three steps in flight, i.e. no action depends
+    on a downloaded result.
+
+    states="lazy" (`e2e`, `e2e_open_loop`): the states cross PCIe row-packed (ceil(d/8) bytes per lattice row)
+    and the host sees the reference's (n,2,d,d) array as a LazyStates view that expands only the envs it indexes.
+    states="u8" (`e2e_u8_full`): the one-byte-per-stabiliser array is expanded on the device and downloaded whole
+    every step -- at 8 ranks the box's aggregate device->host rate (~90 GB/s,
+    profiles/r01_e2e_scale_probe.txt), not the GPUs, bounds that form.
+
     The host policy replays the actions the device's random policy chose on the same seed (recorded beforehand,
     record_device_policy), so the envs walk exactly the trajectory `value` was timed on -- same resets, same
-    perspectives per env -- and the perspective totals are checked against the recording.
-    The perspective tensor stays on the device, where the reference also puts it (`.to(device)`,
-    src/numba/util_actor.py:39).  states="u8" (the `e2e` key) downloads the reference's one-byte-per-stabiliser
-    array; states="rows" (`e2e_state_rows`) downloads np.packbits(states, axis=-1, bitorder="little") instead --
-    at 8 ranks the box's aggregate device->host rate (~90 GB/s, profiles/r01_e2e_scale_probe.txt), not the
-    GPUs, bounds the u8 form."""
+    perspectives per env.  The perspective tensor stays on the device, where the reference also puts it
+    (`.to(device)`, src/numba/util_actor.py:39)."""
     import torch
     from toric_rl_decoder_b200 import HostActorPipeline, sharding
     n = a.envs
     host_actions, rec_sum_p = recorded
     warm = host_actions.shape[0] - a.steps
     eng = make_engine()
-    eng.reset()
-    depth = 3
+    prepare(a, eng)
     pipe = HostActorPipeline(eng, depth=depth, states=states)
-    skey = "states" if states == "u8" else "state_rows"
     checksum = 0.0
+    collected = 0
+    prev_total = 0
+
+    def read(res):
+        nonlocal checksum, collected, prev_total
+        total = prev_total + int(res["counts"].sum(dtype="int64"))
+        assert total == rec_sum_p[collected], "host-buffer run left the recorded trajectory"
+        prev_total = total
+        collected += 1
+        checksum += float(res["reward"][0]) + float(res["states"][0][0, 0, 0])
 
     def run(k0, k1):
-        nonlocal checksum
         for k in range(k0, k1):
             if pipe.submitted - pipe.collected >= depth:
-                res = pipe.collect()                    # the oldest step in flight is in host memory now
-                checksum += float(res["reward"][0]) + float(res[skey][0, 0, 0, 0])
+                read(pipe.collect())                    # the oldest step in flight is in host memory now
             pipe.submit(host_actions[k], auto_reset=True)
         while pipe.collected < pipe.submitted:
-            res = pipe.collect()
-            checksum += float(res["reward"][0])
+            read(pipe.collect())
 
     run(0, warm)
     barrier()
     c0 = eng.counters.clone()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
     ev0.record()
     run(warm, warm + a.steps)
     ev1.record()
+    torch.cuda.synchronize()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
     barrier()
-    ms = ev0.elapsed_time(ev1)
-    ms = sharding.max_over_ranks(ms, dev)
+    ms_raw = ev0.elapsed_time(ev1)
+    ms = sharding.max_over_ranks(ms_raw, dev)
     dc = eng.counters - c0
     assert int(eng.counters[5].item()) == rec_sum_p[-1], "host-buffer run left the recorded trajectory"
     out = {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
            "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
+           "elapsed_ms_raw": ms_raw, "wall_ms": wall_ms, "nonce": _nonce(),
+           "steps_in_flight": depth, "loop": "closed" if depth == 1 else "open",
            "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
-           "call": "HostActorPipeline.submit(pinned host actions) / collect() -> host reward, terminal, counts, "
-                   "%s; uploads and downloads on their own streams, up to 3 steps in flight"
-                   % ("states uint8 (n,2,d,d)" if states == "u8" else
-                      "state_rows uint8 (n,2,d,ceil(d/8)) = packbits(states, little)"),
+           "episodes": int(dc[1].item()),
+           "call": "HostActorPipeline(depth=%d, states=%r).submit(pinned host actions) / collect() -> host reward, "
+                   "terminal, counts, %s; uploads and downloads on their own streams; %s"
+                   % (depth, states,
+                      "states uint8 (n,2,d,d) downloaded whole" if states == "u8" else
+                      "states as a LazyStates view over the row-packed download (ceil(d/8) bytes per lattice row), "
+                      "expanded on the host for the envs that are indexed",
+                      "the next action is submitted only after this step's results were collected and read"
+                      if depth == 1 else "up to %d steps in flight" % depth),
+           "host_touches_per_step": "reward[0]; counts.sum() over all n envs (checked against the recorded "
+                                    "trajectory); states[0] expanded through the view",
            "policy": "host-supplied actions = the device random policy's choices on the same seed (recorded), "
                      "i.e. the trajectory `value` is timed on"}
     del pipe, eng

@@ -151,14 +151,16 @@ class ActorLoop:
             k = min(per, n - base)
             self.slices.append(ActorSlice(d, k, p_error, seed, env_base + base, max_steps))
             base += k
+        self._pool = None
 
     def run(self, steps):
-        import threading
-        ts = [threading.Thread(target=s.run, args=(steps,)) for s in self.slices]
-        for t in ts:
-            t.start()
-        for t in ts:
-            t.join()
+        """Advance every slice by `steps` steps; the worker threads are created once and reused (a fresh
+        thread per call showed up in sub-second timed regions)."""
+        if self._pool is None:
+            from concurrent.futures import ThreadPoolExecutor
+            self._pool = ThreadPoolExecutor(max_workers=len(self.slices))
+        for f in [self._pool.submit(s.run, steps) for s in self.slices]:
+            f.result()
 
     @property
     def counters(self):

@@ -10,6 +10,7 @@ import pytest
 import torch
 
 from oracle import c_oracle as C
+import golden
 from oracle import toric_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -250,7 +251,7 @@ def test_full_size_properties(pkg, d, n):
     assert torch.equal(before, eng.syn)
 
 
-@pytest.mark.parametrize("d,states", ((7, "u8"), (7, "rows"), (13, "rows"), (5, None)))
+@pytest.mark.parametrize("d,states", ((7, "u8"), (7, "rows"), (13, "rows"), (5, None), (7, "lazy"), (25, "lazy")))
 def test_host_pipeline_matches_oracle(pkg, d, states):
     """HostActorPipeline (pinned host actions in, host results out, two steps in flight) == the numpy oracle."""
     n, steps = 300, 12
@@ -263,20 +264,27 @@ def test_host_pipeline_matches_oracle(pkg, d, states):
                      axis=1).astype(np.int32) for _ in range(steps)]
     pinned = [torch.from_numpy(a).pin_memory() for a in acts]
     pipe = pkg.HostActorPipeline(eng, depth=2, states=states)
-    got = []
+    got, probes = [], []
+
+    def take(r):
+        if states == "lazy":                       # the live view, indexed the way a host policy would
+            assert isinstance(r["states"], pkg.hostpipe.LazyStates) and r["states"].shape == (n, 2, d, d)
+            probes.append((r["states"][7].copy(), r["states"][[3, 299], 1].copy(), int(r["states"][5, 0, 1, 2])))
+        got.append({key: np.array(val) for key, val in r.items()})
     for k in range(steps):
         pipe.submit(pinned[k], auto_reset=False)
         if k > 0:
-            r = pipe.collect()
-            got.append({key: np.array(val) for key, val in r.items()})
-    r = pipe.collect()
-    got.append({key: np.array(val) for key, val in r.items()})
+            take(pipe.collect())
+    take(pipe.collect())
     for k in range(steps):
         for e in range(n):
             q[e], s[e], rew, term = O.step(q[e], s[e], acts[k][e])
             assert got[k]["reward"][e] == rew and bool(got[k]["terminal"][e]) == term
-        if states == "u8":
-            assert (got[k]["states"] == s).all()
+        if states in ("u8", "lazy"):
+            assert got[k]["states"].shape == s.shape and (got[k]["states"] == s).all()
+            if states == "lazy":
+                assert (probes[k][0] == s[7]).all() and (probes[k][1] == s[[3, 299], 1]).all()
+                assert probes[k][2] == s[5, 0, 1, 2]
         elif states == "rows":
             assert (got[k]["state_rows"] == np.packbits(s.astype(np.uint8), axis=-1, bitorder="little")).all()
             assert (pipe.unpack_rows(got[k]["state_rows"]) == s).all()
@@ -284,6 +292,27 @@ def test_host_pipeline_matches_oracle(pkg, d, states):
             assert "states" not in got[k] and "state_rows" not in got[k]
         _, _, counts, _ = O.perspectives_batch(s)
         assert (got[k]["counts"] == counts).all()
+
+
+def test_host_pipeline_lazy_states_equal_envset_golden(pkg):
+    """The lazy `states` view of the closed-loop host pipeline (one step in flight: the next action is submitted
+    only after the previous step was collected) equals what EnvSet.step returned in the reference's own recorded
+    run (src/EnvSet.py:38-47; tests/golden/golden_batch_d7.npz), rewards and terminals included."""
+    g = golden.batch_d7()
+    n = len(g["qubits0"])
+    eng = pkg.ToricEngine(7, n, seed=0, p_error=0.1, max_steps=1000)
+    eng.set_qubits(g["qubits0"])
+    pipe = pkg.HostActorPipeline(eng, depth=1)           # states="lazy" is the default
+    for t in range(g["actions"].shape[0]):
+        res = pipe.step(torch.from_numpy(g["actions"][t].astype(np.int32)).pin_memory(), auto_reset=False)
+        st = res["states"]
+        assert st.shape == g["states"][t].shape
+        assert (np.asarray(st) == g["states"][t]).all()
+        for e in (0, 17, n - 1):
+            assert (st[e] == g["states"][t][e]).all()
+        assert (res["reward"].astype(np.float64) == g["rewards"][t]).all()
+        assert (res["terminal"] == g["terminals"][t]).all()
+        assert res["state_rows"].nbytes * 7 == np.asarray(st).nbytes      # 1 byte per lattice row crosses PCIe at d=7
 
 
 @pytest.mark.parametrize("d,n", ((7, 3000), (15, 200)))

@@ -14,4 +14,4 @@ from .policy import (calculateEpsilon, computePriorities, computePrioritiesParal
                      generatePerspectiveParallel, generateTransition, generateTransitionParallel,
                      predictMaxOptimized, rotate_state, selectAction, selectActionBatch, selectActionParallel,
                      select_action_device, shift_state, transitions_device)
-from .hostpipe import HostActorPipeline  # noqa: F401
+from .hostpipe import HostActorPipeline, LazyStates  # noqa: F401

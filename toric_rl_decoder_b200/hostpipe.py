@@ -23,16 +23,70 @@ from . import _lib
 from .engine import _ptr
 
 
+class LazyStates:
+    """The `states` array of EnvSet.step (src/EnvSet.py:39,47: (n,2,d,d) of 0/1) kept on the host in its
+    row-packed download format and expanded only where a caller looks.
+
+    Indexing follows numpy: the first index selects envs (int, slice, integer / boolean array) and is applied to
+    the packed rows, the selected envs are expanded to uint8 0/1, the remaining indices are applied to that.
+    `np.asarray(view)` / `view.astype(...)` expand every env.  The view aliases the pipeline's pinned download
+    slot: it is valid until that slot is reused (`depth` submits later); `copy()` detaches it."""
+
+    dtype = np.dtype(np.uint8)
+    ndim = 4
+
+    def __init__(self, rows, d):
+        self._rows, self._d = rows, int(d)
+        self.shape = (rows.shape[0], 2, self._d, self._d)
+
+    def __len__(self):
+        return self.shape[0]
+
+    def _expand(self, rows):
+        return np.unpackbits(rows, axis=-1, count=self._d, bitorder="little")
+
+    def __getitem__(self, idx):
+        first, rest = (idx[0], idx[1:]) if isinstance(idx, tuple) and len(idx) else (idx, ())
+        if first is Ellipsis or (isinstance(idx, tuple) and not len(idx)):
+            return np.asarray(self)[idx]
+        sub = self._expand(self._rows[first])
+        if not rest:
+            return sub
+        if isinstance(first, (int, np.integer)):
+            return sub[rest]
+        return sub[(slice(None),) + tuple(rest)]
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._expand(self._rows)
+        return a if dtype is None else a.astype(dtype, copy=False)
+
+    def astype(self, dtype):
+        return np.asarray(self).astype(dtype)
+
+    def copy(self):
+        return LazyStates(self._rows.copy(), self._d)
+
+    @property
+    def packed_rows(self):
+        """uint8 (n,2,d,ceil(d/8)) = np.packbits(states, axis=-1, bitorder="little")."""
+        return self._rows
+
+
 class HostActorPipeline:
-    def __init__(self, engine, depth=2, states="u8"):
+    def __init__(self, engine, depth=2, states="lazy"):
         """states: how each step's new states reach the host (rewards, terminals and perspective counts
         always do):
-          "u8"   uint8 (n,2,d,d) of 0/1 -- the reference's array (src/EnvSet.py:39,47), one byte per stabiliser;
-          "rows" uint8 (n,2,d,ceil(d/8)) = np.packbits(states, axis=-1, bitorder="little") -- 7x fewer PCIe
-                 bytes at d=7 (`unpack_rows` restores the (n,2,d,d) array);
+          "lazy" (default) the row-packed form crosses PCIe (ceil(d/8) bytes per lattice row, 7x fewer bytes than
+                 one byte per stabiliser at d=7) and `collect()["states"]` is a `LazyStates` view with the
+                 reference's (n,2,d,d) shape that expands rows -> 0/1 bytes on the host only for the envs a
+                 caller indexes;
+          "u8"   uint8 (n,2,d,d) of 0/1 -- the reference's array (src/EnvSet.py:39,47), one byte per stabiliser,
+                 expanded on the device and downloaded whole (PCIe-bound beyond ~2 GPUs per host);
+          "rows" uint8 (n,2,d,ceil(d/8)) = np.packbits(states, axis=-1, bitorder="little") as `state_rows`
+                 (`unpack_rows` restores the (n,2,d,d) array);
           None   states stay on the device."""
-        if states not in ("u8", "rows", None):
-            raise ValueError('states must be "u8", "rows" or None')
+        if states not in ("lazy", "u8", "rows", None):
+            raise ValueError('states must be "lazy", "u8", "rows" or None')
         self.eng = engine
         self.depth = int(depth)
         self.states = states
@@ -45,7 +99,8 @@ class HostActorPipeline:
         self.o_term = 8 * n
         self.o_state = (9 * n + 15) & ~15
         self.row_bytes = (d + 7) // 8
-        self.state_bytes = {"u8": n * 2 * d * d, "rows": n * 2 * d * self.row_bytes, None: 0}[states]
+        self.state_bytes = {"u8": n * 2 * d * d, "rows": n * 2 * d * self.row_bytes,
+                            "lazy": n * 2 * d * self.row_bytes, None: 0}[states]
         self.nbytes = self.o_state + self.state_bytes
         self.h2d_bytes = n * 16
         self.d2h_bytes = self.nbytes
@@ -67,9 +122,11 @@ class HostActorPipeline:
             }
             if states == "u8":
                 slot["views"]["states"] = hs[self.o_state:self.o_state + self.state_bytes].reshape(n, 2, d, d)
-            elif states == "rows":
-                slot["views"]["state_rows"] = hs[self.o_state:self.o_state + self.state_bytes].reshape(
-                    n, 2, d, self.row_bytes)
+            elif states in ("rows", "lazy"):
+                rows = hs[self.o_state:self.o_state + self.state_bytes].reshape(n, 2, d, self.row_bytes)
+                slot["views"]["state_rows"] = rows
+                if states == "lazy":
+                    slot["views"]["states"] = LazyStates(rows, d)
             ds = slot["d_stage"]
             slot["d_reward"] = ds[self.o_reward:self.o_reward + 4 * n].view(torch.float32)
             slot["d_counts"] = ds[self.o_counts:self.o_counts + 4 * n].view(torch.int32)
@@ -108,7 +165,7 @@ class HostActorPipeline:
             if self.states == "u8":
                 _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
                                                    self.d2h_stream.cuda_stream), "tc_unpack_state")
-            elif self.states == "rows":
+            elif self.states in ("rows", "lazy"):
                 _lib.check(eng.lib.tc_state_rows(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
                                                  self.d2h_stream.cuda_stream), "tc_state_rows")
             if self.states is not None:
@@ -120,8 +177,9 @@ class HostActorPipeline:
 
     def collect(self):
         """Block until the oldest outstanding step's results are in host memory; returns numpy views
-        {reward f32 (n,), counts i32 (n,), terminal bool (n,), states u8 (n,2,d,d) | state_rows u8
-        (n,2,d,ceil(d/8))} valid until the slot is reused (depth submits later)."""
+        {reward f32 (n,), counts i32 (n,), terminal bool (n,), states (n,2,d,d) -- a LazyStates view ("lazy") or
+        a uint8 array ("u8") -- and/or state_rows u8 (n,2,d,ceil(d/8))} valid until the slot is reused (depth
+        submits later)."""
         if self.collected >= self.submitted:
             raise RuntimeError("nothing to collect")
         slot = self.slots[self.collected % self.depth]
