@@ -269,6 +269,7 @@ def run_b200(a):
     eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p,
                           out_dtype=out_dtype)                                              # envs shard by rank
     eng.ensure_capacity(eng.worst_case_capacity())
+    max_steps = eng.max_steps
     prepare(a, eng)                             # reset, staggered episode clocks, untimed burn-in
 
     def barrier():
@@ -380,7 +381,7 @@ def run_b200(a):
                            "global_envs": n * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
                            "mean_perspectives_per_env": p_bar, "out_dtype": a.out_dtype,
                            "regime": ("stationary: episode clocks staggered over [0, %d], %d untimed burn-in steps "
-                                      "before the warm-up" % (eng.max_steps, a.burnin)) if not a.no_stagger else
+                                      "before the warm-up" % (max_steps, a.burnin)) if not a.no_stagger else
                                      "all envs start their first episode at the first warm-up step",
                            "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
                                  % (wbytes / 1e9),

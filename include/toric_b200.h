@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 3
+#define TC_ABI_VERSION 4
 #define TC_NUM_COUNTERS 16
 
 /* status bits written per env */
@@ -47,6 +47,11 @@ extern "C" {
 #define TC_ACTOR_RANDOM_ACTIONS 1 /* draw the action on device (uniform over the perspective list x {X,Y,Z}) */
 #define TC_ACTOR_AUTO_RESET 2     /* reset envs that are terminal or past max_steps (Actor_mp.py:171-183) */
 #define TC_ACTOR_FREEZE_DONE 4    /* leave already-solved envs untouched (batched evaluation.py:79 loop exit) */
+#define TC_ACTOR_SINGLE_PASS 8    /* tc_actor_step only: ONE kernel (step + cross-env scan by decoupled look-back +
+                                   * perspective writer) instead of three; same results bit for bit.  d <=
+                                   * TC_SINGLE_PASS_MAX_D; the workspace must have been zero-filled once before its
+                                   * first use (it carries the look-back descriptors from launch to launch). */
+#define TC_SINGLE_PASS_MAX_D 16
 
 /* element types of tc_transitions outputs */
 #define TC_DTYPE_F32 0
@@ -133,6 +138,13 @@ int tc_perspectives_as(const uint32_t* syn, void* out, int out_dtype, uint8_t* p
  *   steps       int32 [n]     steps taken in the current episode
  *   counters    int64 [TC_NUM_COUNTERS] running totals, nullable
  *   prev_syn    uint32 [n][2][d] copy of the pre-reset post-step syndrome (transition next_state), nullable
+ *   gs          uint8 [n]     out, a per-step RESULT like reward / terminal: 1 iff all four plane parities are
+ *                             even after this step and before any auto-reset, i.e. what evalGroundState
+ *                             (ToricCode.py:326-335) returns on the post-step state with a fresh flag -- for an
+ *                             episode that ends in this step it is the episode's logical outcome.  It is
+ *                             OVERWRITTEN every step (not AND-ed) and not touched for frozen envs, so it is not
+ *                             the sticky flag of tc_ground_state / tc_reset: pass a different buffer when both
+ *                             interfaces are used on the same envs (ToricEngine: `step_gs` vs `gs`).
  */
 int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
                   uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,

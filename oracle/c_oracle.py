@@ -35,6 +35,8 @@ def load():
         lib.to_philox4x32_10.restype = None
         lib.to_reset.argtypes = [vp, vp, i, u64, u32, u32, i, i, u64]
         lib.to_reset.restype = u32
+        lib.to_reset_batch.argtypes = [vp, vp, i, i64, u64, u32, u32, i, i, u64, vp]
+        lib.to_reset_batch.restype = None
         lib.to_random_action.argtypes = [vp, i, u64, u32, u32, u64, vp, vp]
         lib.to_random_action.restype = None
         lib.to_actor_steps.argtypes = [vp, vp, vp, vp, vp, i64, i, i, i, u64, i64, vp, vp, i64, vp, vp]
@@ -98,6 +100,15 @@ def reset(d, env_id, episode, thresh, seed, mode=0, n_fixed=0):
     return q, s, int(att)
 
 
+def reset_batch(d, n, env_base, episode, thresh, seed, mode=0, n_fixed=0):
+    """to_reset for envs env_base .. env_base+n-1: (qubits u8 (n,2,d,d), syndromes u8 (n,2,d,d), attempts u32 (n,))."""
+    q = np.zeros((n, 2, d, d), np.uint8)
+    s = np.zeros((n, 2, d, d), np.uint8)
+    att = np.zeros(n, np.uint32)
+    load().to_reset_batch(_p(q), _p(s), d, n, int(env_base), int(episode), int(thresh), mode, n_fixed, int(seed), _p(att))
+    return q, s, att
+
+
 def random_action(s, env_id, episode, step_no, seed):
     s = np.ascontiguousarray(s, dtype=np.uint8)
     d = s.shape[-1]
@@ -124,8 +135,7 @@ class ActorSlice:
         self.pos = np.zeros((self.cap, 3), np.int32)
         self.offsets = np.zeros(n + 1, np.int64)
         self.counters = np.zeros(4, np.int64)
-        for e in range(n):
-            self.lib.to_reset(_p(self.q[e]), _p(self.s[e]), d, env_base + e, 0, th, 0, 0, seed)
+        self.lib.to_reset_batch(_p(self.q), _p(self.s), d, n, env_base, 0, th, 0, 0, seed, None)
         self.episode[:] = 1
 
     def run(self, steps):

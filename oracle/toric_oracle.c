@@ -14,6 +14,7 @@
  * (DESIGN.md "RNG"): the reference uses numpy's MT19937, which a counter-based device generator cannot
  * and need not reproduce; its distribution is validated statistically instead.
  */
+#include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -122,11 +123,69 @@ static inline uint32_t mulhi(uint32_t a, uint32_t b) { return (uint32_t)(((uint6
 #define DOM_FIXED 0x80000000u
 #define DOM_ACTION 0xC0000000u
 
-/* ToricCode.reset's sampling loop (ToricCode.py:108-117) with the device's draw numbering.
- * mode 0: generateRandomError (:130-151)   error iff u < thresh, code = 1 + mulhi(c,3)
- * mode 1: generateNRandomErrors (:153-166) n_fixed distinct qubits, rejection on occupied
- * mode 2: generateNPlusQRandomErrors (results/small_p_error_test.py:43-52)
- * Returns the number of attempts (0x80000000 | attempts if the cap was hit). */
+#define DOM_FIRST 0x40000000u
+
+/* Depolarizing field of one lattice row, both matrices (csrc/sampler.cuh:depolarize_row).  Qubit s = m*d + j of
+ * the row owns the 16-bit slot s (bits [16*(s%8), +16) of call s/8); error iff the lazily extended 32-bit uniform
+ * is below thresh; the codes of the row's errors are 2-bit chunks (0 rejected) from the stream behind the last
+ * slot.  first_q >= 0: linear index q = m*d*d + i*d + j of the forced first error (qubits before it stay clean). */
+static void depolarize_row(uint8_t* field /* [2][d][d], written for row `row` only */, int d, int row,
+                           uint64_t env_id, uint32_t episode, uint32_t attempt, uint32_t thresh,
+                           const uint32_t key[2], int first_q) {
+  const uint32_t t_hi = thresh >> 16, t_lo = thresh & 0xffffu;
+  const uint32_t base = (attempt << 10) | ((uint32_t)row << 5);
+  const int nslots = 2 * d, ncalls = (nslots + 7) / 8;
+  uint8_t err[64];
+  uint32_t rnd[4] = {0, 0, 0, 0};
+  for (int s = 0; s < nslots; ++s) {
+    if ((s & 7) == 0) {
+      const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, base | (uint32_t)(s >> 3)};
+      to_philox4x32_10(ctr, key, rnd);
+    }
+    const int h = s & 7;
+    const uint32_t w = rnd[h >> 1];
+    const uint32_t u = (h & 1) ? (w >> 16) : (w & 0xffffu);
+    err[s] = (uint8_t)(u < t_hi);
+    if (u == t_hi) {                              /* draw the low half of the uniform */
+      const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, base | (uint32_t)(16 + (s >> 2))};
+      uint32_t r2[4];
+      to_philox4x32_10(ctr, key, r2);
+      err[s] = (uint8_t)((r2[s & 3] & 0xffffu) < t_lo);
+    }
+  }
+  if (first_q >= 0)
+    for (int s = 0; s < nslots; ++s) {
+      const int m = s / d, j = s - m * d, q = (m * d + row) * d + j;
+      if (q < first_q) err[s] = 0;
+      if (q == first_q) err[s] = 1;
+    }
+  int c = ncalls - 1, pos = 16 * (nslots & 7);
+  if (pos == 0) pos = 128;
+  for (int s = 0; s < nslots; ++s) {
+    const int m = s / d, j = s - m * d;
+    uint32_t v = 0;
+    if (err[s]) {
+      do {
+        if (pos >= 128) {
+          ++c;
+          const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, base | (uint32_t)(c & 15)};
+          to_philox4x32_10(ctr, key, rnd);
+          pos = 0;
+        }
+        v = (rnd[pos >> 5] >> (pos & 31)) & 3u;
+        pos += 2;
+      } while (v == 0);
+    }
+    field[IDX(m, row, j)] = (uint8_t)v;           /* 0 = no error, else the Pauli code */
+  }
+}
+
+/* ToricCode.reset's sampling loop (ToricCode.py:108-117) with the device's draw numbering (csrc/sampler.cuh).
+ * mode 0: generateRandomError (:130-151)   mode 1: generateNRandomErrors (:153-166), n_fixed distinct qubits
+ * mode 2: generateNPlusQRandomErrors (results/small_p_error_test.py:43-52);  mode | 16: one draw, no rejection.
+ * When thresh * 2d^2 < 2^32 mode 0 draws the field conditioned on >= 1 error (first-error index from a
+ * truncated geometric law), which leaves the distribution after the rejection unchanged.
+ * Returns the number of attempts (0x80000000 | attempts if the sampler gave up). */
 uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episode, uint32_t thresh, int mode,
                   int n_fixed, uint64_t seed) {
   const uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
@@ -138,7 +197,19 @@ uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episo
   while ((int)pm < nq) pm <<= 1;
   pm -= 1;
   const uint32_t cap = mode == 0 ? (1u << 20) : (1u << 10);
+  const int conditioned = mode == 0 && !one_draw && (uint64_t)thresh * (uint64_t)nq < (1ull << 32);
   uint32_t attempt = 0, rnd[4];
+  uint8_t field[2 * 32 * 32];
+  if (conditioned && thresh == 0) {
+    memset(q, 0, (size_t)nq);
+    memset(s, 0, (size_t)nq);
+    return 0x80000000u | 1u;
+  }
+  double log_q = 0.0, mass = 0.0;
+  if (conditioned) {
+    log_q = log1p(-(double)thresh * (1.0 / 4294967296.0));
+    mass = -expm1((double)nq * log_q);
+  }
   for (;;) {
     memset(q, 0, (size_t)nq);
     if (mode != 0) {
@@ -146,7 +217,7 @@ uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episo
       uint32_t t = 0;
       while (placed < nf) {
         const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode,
-                                 DOM_FIXED | ((attempt & 1023u) << 20) | (t & 0xfffffu)};
+                                 DOM_FIXED | ((attempt & 511u) << 20) | (t & 0xfffffu)};
         to_philox4x32_10(ctr, key, rnd);
         ++t;
         const int qi = (int)(rnd[0] & pm);
@@ -156,21 +227,34 @@ uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episo
       }
     }
     if (mode != 1) {
-      for (int m = 0; m < 2; ++m)
-        for (int i = 0; i < d; ++i)
-          for (int k = 0; k < (d + 1) / 2; ++k) {
-            const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode,
-                                     (attempt << 10) | ((uint32_t)m << 9) | ((uint32_t)i << 4) | (uint32_t)k};
-            to_philox4x32_10(ctr, key, rnd);
-            const int j0 = 2 * k, j1 = 2 * k + 1;
-            if (rnd[0] < thresh && !q[IDX(m, i, j0)]) q[IDX(m, i, j0)] = (uint8_t)(1u + mulhi(rnd[1], 3u));
-            if (j1 < d && rnd[2] < thresh && !q[IDX(m, i, j1)]) q[IDX(m, i, j1)] = (uint8_t)(1u + mulhi(rnd[3], 3u));
-          }
+      int first_q = -1;
+      if (conditioned) {
+        const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, DOM_FIRST | attempt};
+        to_philox4x32_10(ctr, key, rnd);
+        const uint64_t u53 = (((uint64_t)rnd[0] << 32) | (uint64_t)rnd[1]) >> 11;
+        const double u = (double)u53 * (1.0 / 9007199254740992.0);
+        const double k = floor(log1p(-u * mass) / log_q);
+        first_q = k >= (double)(nq - 1) ? nq - 1 : (k > 0.0 ? (int)k : 0);
+      }
+      for (int i = 0; i < d; ++i) depolarize_row(field, d, i, env_id, episode, attempt, thresh, key, first_q);
+      for (int k = 0; k < nq; ++k)
+        if (!q[k]) q[k] = field[k];               /* occupied qubits keep the fixed part's code */
     }
     to_syndrome(q, s, d);
     ++attempt;
     if (defects(s, d) != 0 || one_draw) return attempt;
     if (attempt >= cap) return 0x80000000u | attempt;
+  }
+}
+
+/* to_reset over a batch of envs (ids env_base .. env_base+n-1, same episode / thresh); q, s: uint8 [n][2][d][d];
+ * attempts (nullable): uint32 [n] return values of to_reset. */
+void to_reset_batch(uint8_t* q, uint8_t* s, int d, int64_t n, uint64_t env_base, uint32_t episode, uint32_t thresh,
+                    int mode, int n_fixed, uint64_t seed, uint32_t* attempts) {
+  const int nq = 2 * d * d;
+  for (int64_t e = 0; e < n; ++e) {
+    const uint32_t a = to_reset(q + e * nq, s + e * nq, d, env_base + (uint64_t)e, episode, thresh, mode, n_fixed, seed);
+    if (attempts) attempts[e] = a;
   }
 }
 

@@ -11,6 +11,7 @@ import torch
 
 from oracle import c_oracle as C
 import golden
+import sampler_checks as S
 from oracle import toric_oracle as O
 
 pytestmark = pytest.mark.gpu
@@ -23,7 +24,9 @@ def pkg(cuda_device):
 
 
 @pytest.mark.parametrize("d,mode,n_fixed,p", ((7, 0, 0, 0.1), (5, 0, 0, 0.003), (9, 1, 5, 0.1), (7, 2, 4, 0.05),
-                                               (16, 0, 0, 0.02), (25, 0, 0, 0.05), (3, 1, 18, 0.1), (32, 2, 7, 0.01)))
+                                               (16, 0, 0, 0.02), (25, 0, 0, 0.05), (3, 1, 18, 0.1), (32, 2, 7, 0.01),
+                                               (7, 0, 0, 0.0005), (7, 0, 0, 0.0103), (32, 0, 0, 0.2), (3, 0, 0, 0.3),
+                                               (25, 0, 0, 0.0001), (8, 0, 0, 0.1), (4, 2, 2, 0.3), (7, 0, 0, 0.99)))
 def test_reset_matches_sampler_spec(pkg, d, mode, n_fixed, p):
     n, seed, base = 96, 4242, 1000
     eng = pkg.ToricEngine(d, n, seed=seed, env_base=base, p_error=p)
@@ -82,12 +85,17 @@ def test_bare_generators(pkg):
         assert abs((q == c).mean() - 0.1 / 3) < 5 * np.sqrt(0.0333 * 0.9667 / q.size)
 
 
+@pytest.mark.parametrize("single_pass", (False, True))
 @pytest.mark.parametrize("d,n,steps,max_steps,p", ((7, 512, 100, 75, 0.1), (5, 384, 60, 4, 0.02), (9, 128, 30, 10, 0.1),
-                                                    (4, 64, 40, 6, 0.1), (17, 48, 12, 5, 0.05)))
-def test_fused_actor_trajectory_bit_exact(pkg, d, n, steps, max_steps, p):
-    """tc_actor_step (random actions, auto-reset) == the C oracle's actor loop, every step."""
+                                                    (4, 64, 40, 6, 0.1), (17, 48, 12, 5, 0.05), (7, 1000, 30, 5, 0.003),
+                                                    (3, 77, 20, 3, 0.2), (16, 33, 8, 3, 0.1), (8, 2051, 10, 4, 0.1)))
+def test_fused_actor_trajectory_bit_exact(pkg, d, n, steps, max_steps, p, single_pass):
+    """tc_actor_step (random actions, auto-reset) == the C oracle's actor loop, every step -- in its three-kernel
+    form and in the single-pass form (TC_ACTOR_SINGLE_PASS: one kernel, offsets by decoupled look-back)."""
     seed, base = 11, 7 * n
-    eng = pkg.ToricEngine(d, n, seed=seed, env_base=base, p_error=p, max_steps=max_steps)
+    if single_pass and d > 16:
+        pytest.skip("single-pass step: d <= 16")
+    eng = pkg.ToricEngine(d, n, seed=seed, env_base=base, p_error=p, max_steps=max_steps, single_pass=single_pass)
     eng.reset()
     ref = C.ActorSlice(d, n, p, seed=seed, env_base=base, max_steps=max_steps)
     assert (eng.get_qubits().cpu().numpy() == ref.q).all()
@@ -123,7 +131,7 @@ def test_actor_step_host_policy_and_prev_state(pkg):
         steps_before = eng.steps.cpu().numpy().copy()
         eng.actor_step(actions=torch.from_numpy(acts), auto_reset=True, keep_prev=True)
         prev = eng.get_state(eng.prev_syn).cpu().numpy()
-        rw, tm, gs = eng.reward.cpu().numpy(), eng.terminal.cpu().numpy(), eng.gs.cpu().numpy()
+        rw, tm, gs = eng.reward.cpu().numpy(), eng.terminal.cpu().numpy(), eng.step_gs.cpu().numpy()
         q_now = eng.get_qubits().cpu().numpy().astype(np.int64)
         s_now = eng.get_state().cpu().numpy().astype(np.int64)
         for e in range(n):
@@ -192,6 +200,46 @@ def test_device_rng_statistics(pkg, p):
     assert bool((s.reshape(n, -1).sum(dim=1) > 0).all())
     c = eng.read_counters()
     assert c["env_steps"] == 0
+
+
+@pytest.mark.parametrize("d,p,n", ((7, 0.1, 400000), (7, 0.005, 1 << 20), (7, 0.0005, 1 << 20), (5, 0.0005, 1 << 20),
+                                   (7, 0.0101, 400000), (7, 0.0103, 400000), (15, 0.05, 40000)))
+def test_device_depolarizing_law(pkg, d, p, n):
+    """The device sampler against the law of ToricCode.reset (ToricCode.py:108-117, :130-151) at the low error rates of
+    BASELINE configs[3] too: weight histogram = Binomial(2d^2, p) given a non-trivial syndrome, uniform sites and
+    codes, truncated-geometric first-error position; p = 0.0101 / 0.0103 straddle the switch between the sampler
+    conditioned on >= 1 error and the plain rejection loop (csrc/sampler.cuh)."""
+    eng = pkg.ToricEngine(d, n, seed=31, p_error=p)
+    eng.reset()
+    q = eng.get_qubits().cpu().numpy()
+    s = eng.get_state()
+    assert bool((s.reshape(n, -1).sum(dim=1) > 0).all())
+    assert int((eng.status & 2).sum().item()) == 0
+    S.check_depolarizing(q, p)
+    S.check_first_error_position(q, p)
+
+
+@pytest.mark.parametrize("d,k,n", ((5, 3, 400000), (3, 2, 100000), (7, 1, 100000)))
+def test_device_fixed_weight_law(pkg, d, k, n):
+    """generateNRandomErrors (ToricCode.py:153-166): a uniform random k-subset -- exact count, site uniformity,
+    site-PAIR uniformity, code uniformity."""
+    eng = pkg.ToricEngine(d, n, seed=32, p_error=0.1)
+    eng.reset(mode=pkg.SAMPLE_FIXED_WEIGHT, n_fixed=k)
+    S.check_fixed_weight(eng.get_qubits().cpu().numpy(), k)
+
+
+@pytest.mark.parametrize("d,k,p,n", ((7, 4, 0.005, 400000), (5, 3, 0.05, 200000)))
+def test_device_n_plus_q_law(pkg, d, k, p, n):
+    """generateNPlusQRandomErrors (results/small_p_error_test.py:43-52): q fixed errors + Binomial(2d^2 - q, p)."""
+    eng = pkg.ToricEngine(d, n, seed=33, p_error=p)
+    eng.reset(mode=pkg.SAMPLE_FIXED_PLUS_P, n_fixed=k)
+    S.check_n_plus_q(eng.get_qubits().cpu().numpy(), k, p)
+
+
+def test_reset_p_zero_gives_up_at_once(pkg):
+    eng = pkg.ToricEngine(5, 64, seed=1, p_error=0.0)
+    eng.reset()
+    assert not eng.get_qubits().any() and bool((eng.status & 2).all())
 
 
 def _torch_reference_perspectives(state, pos, env_of, d):
@@ -315,13 +363,60 @@ def test_host_pipeline_lazy_states_equal_envset_golden(pkg):
         assert res["state_rows"].nbytes * 7 == np.asarray(st).nbytes      # 1 byte per lattice row crosses PCIe at d=7
 
 
+@pytest.mark.parametrize("d,n,steps", ((7, 65536, 40), (5, 100003, 12), (9, 20000, 8), (13, 3000, 6), (7, 1, 30), (7, 33, 30)))
+def test_single_pass_step_equals_three_kernel_step(pkg, d, n, steps):
+    """The single-pass step at BASELINE configs[1] size (and ragged / tiny / row-path sizes): every buffer the step
+    touches -- states, results, counters, counts, offsets, positions, perspectives -- equals the three-kernel
+    step's after every step; with host-supplied actions, kept previous syndromes and frozen envs too."""
+    a = pkg.ToricEngine(d, n, seed=3, p_error=0.1, max_steps=9)
+    b = pkg.ToricEngine(d, n, seed=3, p_error=0.1, max_steps=9, single_pass=True)
+    for e in (a, b):
+        e.reset()
+    rng = np.random.default_rng(d)
+    for t in range(steps):
+        kw = {}
+        if t % 3 == 1:                       # host policy + the transition's pre-reset syndrome
+            acts = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n),
+                             rng.integers(0, 5, n)], 1)      # op 4 = a bad action, masked and counted
+            kw = dict(actions=torch.from_numpy(acts), keep_prev=True)
+        if t % 4 == 3:
+            kw["freeze_done"] = True
+            kw["auto_reset"] = False
+        a.actor_step(**kw)
+        b.actor_step(**kw)
+        for name in ("qubits", "syn", "reward", "terminal", "step_gs", "status", "steps", "episode", "counts",
+                     "actions", "counters", "overflow"):
+            assert torch.equal(getattr(a, name), getattr(b, name)), (t, name)
+        if "keep_prev" in kw:
+            assert torch.equal(a.prev_syn, b.prev_syn)
+        if t % 5 == 0 or t == steps - 1:
+            for x, y in zip(a.perspective_views(), b.perspective_views()):
+                assert torch.equal(x, y), t
+    assert a.read_counters()["episodes"] > 0 or n < 10
+
+
+def test_single_pass_step_capacity_overflow_flag(pkg):
+    eng = pkg.ToricEngine(7, 500, seed=1, p_error=0.1, single_pass=True)
+    eng.reset()
+    eng.ensure_capacity(1000)                       # far below sum P
+    eng.actor_step()
+    torch.cuda.synchronize()
+    assert int(eng.overflow.item()) == 1
+    persp, pos, counts, offsets = eng.perspective_views()       # regenerates into a large enough buffer
+    ref = pkg.ToricEngine(7, 500, seed=1, p_error=0.1)
+    ref.reset()
+    ref.actor_step()
+    for x, y in zip((persp, pos, counts, offsets), ref.perspective_views()):
+        assert torch.equal(x, y)
+
+
 @pytest.mark.parametrize("d,n", ((7, 3000), (15, 200)))
 def test_cuda_graph_replay_equals_eager(pkg, d, n):
     """k fused steps captured into a CUDA graph (PDL edges included) and replayed == the same steps launched
     eagerly: states, counters, perspectives."""
     a = pkg.ToricEngine(d, n, seed=11, p_error=0.1, max_steps=6)
-    b = pkg.ToricEngine(d, n, seed=11, p_error=0.1, max_steps=6)
-    for e in (a, b):
+    b = pkg.ToricEngine(d, n, seed=11, p_error=0.1, max_steps=6, single_pass=(d == 7))   # graph replays reuse the
+    for e in (a, b):                                       # kernel arguments: the look-back epoch lives on the device
         e.reset()
     for _ in range(20):
         a.actor_step()

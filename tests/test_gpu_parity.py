@@ -101,6 +101,26 @@ def test_envset_mirror_golden(pkg):
     assert (persp.cpu().numpy() == g["views"].astype(np.float32)).all()
 
 
+def test_perspective_batch_returns_fresh_tensors(pkg):
+    """generatePerspectiveBatch returns fresh tensors like the reference (src/numba/util_actor.py:56-67): a second
+    call at the same d (perspectives of next_state after state) leaves the first result untouched."""
+    g = golden.batch_d7()
+    s0, s1 = g["states"][0], g["states"][-1]
+    first = pkg.generatePerspectiveBatch(3, 7, s0)
+    snap = [t.clone() for t in first]
+    second = pkg.generatePerspectiveBatch(3, 7, s1)
+    for a, b in zip(first, snap):
+        assert torch.equal(a, b)
+    for a, b in zip(first, second):
+        assert a.data_ptr() != b.data_ptr() or a.numel() == 0
+    want, wpos, wcounts, _ = O.perspectives_batch(s1)
+    assert (second[0].cpu().numpy() == want.astype(np.float32)).all()
+    assert (second[1].cpu().numpy() == wpos).all() and (second[2].cpu().numpy() == wcounts).all()
+    assert first[0].shape[0] == int(first[3][-1].item())           # sized to sum P, not to a worst-case buffer
+    empty = pkg.generatePerspectiveBatch(3, 7, np.zeros((4, 2, 7, 7), np.int64))
+    assert empty[0].shape == (0, 2, 7, 7) and empty[3].tolist() == [0, 0, 0, 0, 0]
+
+
 def test_envset_envs_views(pkg):
     """EnvSet.envs[i] (src/EnvSet.py:14-16): per-env ToricCode surface on one row of the batch; the other envs of
     the batch are not touched by anything done through a view."""

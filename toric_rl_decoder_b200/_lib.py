@@ -39,7 +39,7 @@ SIGNATURES = {
     "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],
 }
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 _lib = None
 
 

@@ -78,6 +78,15 @@ constexpr int kSampleOneDraw = 16;             // TC_SAMPLE_ONE_DRAW (OR-ed into
 // resident while the previous kernel drains and only its reads of the predecessor's results wait.
 // pdl_wait() returns once every prerequisite grid has completed and its writes are visible (a no-op for a
 // normal launch); pdl_launch_dependents() lets the next kernel in the stream start launching.
+//
+// INVARIANT (every kernel launched through launch_pdl): NO EXIT PATH BEFORE pdl_wait().  Ordering across more than
+// one launch is transitive only -- actor(k+1) waits for writer(k), which waited for scan(k), which waited for
+// actor(k) -- and a grid only counts as complete for its dependents once all of its threads have exited; a thread
+// that returned before its own pdl_wait() would let its grid complete while the grid in front of it is still
+// running, and the dependent behind it would then race with that older grid on syn / workspace / offsets.  So an
+// out-of-range thread clamps its index (or skips its work) and still executes pdl_wait().  Kernels launched with the
+// plain <<<>>> syntax (reset_kernel, the policy kernels) take a full stream dependency and may return early.
+// tests/test_gpu_actor.py::test_pdl_chain_matches_serialized_launches compares long chains against a TC_PDL=0 build.
 // ---------------------------------------------------------------------------------------------
 #ifndef TC_PDL
 #define TC_PDL 1

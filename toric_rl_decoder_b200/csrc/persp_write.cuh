@@ -136,38 +136,36 @@ __device__ __forceinline__ uint4 expand_chunk(uint32_t bits, uint32_t one16) {
   }
 }
 
+// Per-warp shared-memory layout of the writer: [stage tiles][tab / planes][pos list][aux]; `cand` is per CTA.
 template <int D, typename OutT>
-__global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
-persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
-                   const int64_t* __restrict__ block_off, int epb, OutT* __restrict__ out,
-                   uint8_t* __restrict__ pos, int64_t* __restrict__ offsets, int32_t* __restrict__ overflow,
-                   int64_t cap, int64_t n, uint32_t one16, int split) {
+struct WriterCtx {
+  OutT* stage;
+  unsigned char* tab_raw;
+  uint16_t* sp;
+  unsigned char* aux;
+  const uint2* cand;
+  int lane;
+  __device__ __forceinline__ WriterCtx(unsigned char* smem, int warp, int lane_) : lane(lane_) {
+    using Cfg = PerspCfg<D>;
+    unsigned char* wb = smem + Cfg::kCandBytes + warp * Cfg::kWarpBytes;
+    stage = reinterpret_cast<OutT*>(wb);
+    tab_raw = wb + kStageBufs * kTileBytes;
+    sp = reinterpret_cast<uint16_t*>(tab_raw + ((Cfg::kTabBytes + 15) & ~15));
+    aux = reinterpret_cast<unsigned char*>(sp) + Cfg::kPosBytes;
+    cand = reinterpret_cast<const uint2*>(smem);
+  }
+};
+
+// per-CTA candidate table (plane path): q = m*d*d + i*d + j -> {plane index | i<<16, position word}
+// plane index = 2m*d*d + r0*d + r1 with (r0,r1) = ((i-g)%d, (j-g)%d) for m=0 and ((g-j)%d, (i-g)%d) for m=1.
+// Ends with a CTA barrier when the table exists.
+template <int D>
+__device__ __forceinline__ void build_cand_table(unsigned char* smem, int nthreads) {
   using Cfg = PerspCfg<D>;
-  using OC = OutCfg<OutT>;
-  constexpr int kE = OC::kE;
-  constexpr int kWordsPerLane = OC::kWordsPerLane;
-  constexpr int kTileElems = OC::kTileElems;
-  using TabT = typename Cfg::TabT;
-  constexpr int G = D / 2;                       // grid_shift (src/Actor_mp.py:59)
-  constexpr int DD = D * D;
-  constexpr uint32_t kFull = 0xffffffffu;
-  constexpr uint32_t kRowMask = D >= 32 ? 0xffffffffu : ((1u << (D & 31)) - 1u);
-  extern __shared__ __align__(128) unsigned char smem[];
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  unsigned char* wb = smem + Cfg::kCandBytes + warp * Cfg::kWarpBytes;
-  OutT* stage = reinterpret_cast<OutT*>(wb);
-  unsigned char* tab_raw = wb + kStageBufs * kTileBytes;
-  uint16_t* sp = reinterpret_cast<uint16_t*>(tab_raw + ((Cfg::kTabBytes + 15) & ~15));
-  unsigned char* aux = reinterpret_cast<unsigned char*>(sp) + Cfg::kPosBytes;
-  uint32_t* pos32 = reinterpret_cast<uint32_t*>(pos);
-
-  // ---- per-CTA candidate table (plane path): q = m*d*d + i*d + j -> {plane index | i<<16, position word} ----
-  // plane index = 2m*d*d + r0*d + r1 with (r0,r1) = ((i-g)%d, (j-g)%d) for m=0 and ((g-j)%d, (i-g)%d) for m=1
-  uint2* cand = reinterpret_cast<uint2*>(smem);
+  constexpr int G = D / 2, DD = D * D;
   if constexpr (Cfg::kPlane) {
-    for (int q = threadIdx.x; q < 2 * DD; q += Cfg::kWarps * 32) {
+    uint2* cand = reinterpret_cast<uint2*>(smem);
+    for (int q = threadIdx.x; q < 2 * DD; q += nthreads) {
       const int m = q >= DD ? 1 : 0;
       const int rem = q - m * DD;
       const int i = rem / D, j = rem - i * D;
@@ -180,6 +178,262 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
     }
     __syncthreads();
   }
+}
+
+// One env (or one slice of its tiles) by one warp: position list, base tables, bit stream -> staging tiles -> TMA
+// bulk stores.  v / pl: the env's syndrome rows (lane r holds row r), m0 / m1 its selection masks, P > 0 its
+// perspective count, off its first perspective's index in `out`.  pos_w: where positions go (nullptr for slices
+// other than 0).  `ring` counts the staging tiles this warp has pushed so far (keeps rotating across envs).
+template <int D, typename OutT>
+__device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t v, uint32_t pl, uint32_t m0,
+                                          uint32_t m1, int P, int64_t off, int slice, int split, uint32_t& ring,
+                                          OutT* __restrict__ out, uint8_t* __restrict__ pos_w, uint32_t one16) {
+  using Cfg = PerspCfg<D>;
+  using OC = OutCfg<OutT>;
+  constexpr int kE = OC::kE;
+  constexpr int kWordsPerLane = OC::kWordsPerLane;
+  constexpr int kTileElems = OC::kTileElems;
+  using TabT = typename Cfg::TabT;
+  constexpr int G = D / 2;                       // grid_shift (src/Actor_mp.py:59)
+  constexpr int DD = D * D;
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr uint32_t kRowMask = D >= 32 ? 0xffffffffu : ((1u << (D & 31)) - 1u);
+  const int lane = cx.lane;
+  OutT* const stage = cx.stage;
+  unsigned char* const tab_raw = cx.tab_raw;
+  uint16_t* const sp = cx.sp;
+  unsigned char* const aux = cx.aux;
+  const uint2* const cand = cx.cand;
+  uint32_t* pos32 = reinterpret_cast<uint32_t*>(pos_w);
+
+  // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
+  // One candidate qubit per lane and round; selected candidates are compacted in order with a ballot.
+  // sp[k]: plane path = index of the c=0 rolled plane of perspective k; row path = m | r0<<1 | r1<<6.
+  {
+    int kbase = 0;
+#pragma unroll 1
+    for (int q0 = 0; q0 < 2 * DD; q0 += 32) {
+      const int q = q0 + lane;
+      if constexpr (Cfg::kPlane) {
+        const uint2 cd = cand[q < 2 * DD ? q : 0];
+        const uint32_t r0m = __shfl_sync(kFull, m0, (cd.x >> 16) & 31u);
+        const uint32_t r1m = __shfl_sync(kFull, m1, (cd.x >> 16) & 31u);
+        const bool sel = q < 2 * DD && ((((cd.x >> 31) ? r1m : r0m) >> ((cd.x >> 24) & 31u)) & 1u);
+        const uint32_t bal = __ballot_sync(kFull, sel);
+        if (sel) {
+          const int k = kbase + __popc(bal & ((1u << lane) - 1u));
+          sp[k] = (uint16_t)cd.x;
+          if (pos_w) pos32[off + k] = cd.y;
+        }
+        kbase += __popc(bal);
+      } else {
+        const int m = q >= DD ? 1 : 0;
+        const int rem = q - m * DD;
+        const int i = rem / D, j = rem - i * D;
+        const uint32_t r0m = __shfl_sync(kFull, m0, i & 31), r1m = __shfl_sync(kFull, m1, i & 31);
+        const bool sel = q < 2 * DD && (((m ? r1m : r0m) >> j) & 1u);
+        const uint32_t bal = __ballot_sync(kFull, sel);
+        if (sel) {
+          const int k = kbase + __popc(bal & ((1u << lane) - 1u));
+          int ia = i - G; if (ia < 0) ia += D;
+          int rj = m ? G - j : j - G; if (rj < 0) rj += D;
+          const int r0 = m ? rj : ia, r1 = m ? ia : rj;
+          sp[k] = (uint16_t)(m | (r0 << 1) | (r1 << 6));
+          if (pos_w) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
+        }
+        kbase += __popc(bal);
+      }
+    }
+  }
+
+  // ---- base tables: t = 2m + c; row a of table t (see header) ----
+  uint32_t tv = 0, tp = 0;
+#pragma unroll
+  for (int b = 0; b < D; ++b) {
+    const uint32_t bv = __ballot_sync(kFull, (v >> b) & 1u);
+    const uint32_t bp = __ballot_sync(kFull, (pl >> b) & 1u);
+    if (lane == b) { tv = bv; tp = bp; }
+  }
+  if constexpr (Cfg::kPlane) {
+    unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw);
+    uint32_t* rows = reinterpret_cast<uint32_t*>(aux);                         // [4][16]: rows doubled
+    if (lane < D) {
+      const int kv = (D - lane) % D, kp = D - 1 - lane;
+      rows[0 * 16 + lane] = v;
+      rows[0 * 16 + lane + D] = v;
+      rows[1 * 16 + lane] = pl;
+      rows[1 * 16 + lane + D] = pl;
+      rows[2 * 16 + kv] = tv & kRowMask;
+      rows[2 * 16 + kv + D] = tv & kRowMask;
+      rows[3 * 16 + kp] = tp & kRowMask;
+      rows[3 * 16 + kp + D] = tp & kRowMask;
+    }
+    __syncwarp();
+    if (lane < 4 * D) {
+      // lane = t*d + r0: row-rolled plane x[a] = T[t][(a + r0) % d], then the d column rolls
+      const int t = lane / D, r0 = lane - t * D;
+      unsigned long long x = 0;
+#pragma unroll
+      for (int a = 0; a < D; ++a) x |= (unsigned long long)rows[t * 16 + a + r0] << (a * D);
+      constexpr unsigned long long kMaskDD = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
+      unsigned long long rep = 0;
+#pragma unroll
+      for (int a = 0; a < D; ++a) rep |= 1ull << (a * D);
+#pragma unroll
+      for (int r1 = 0; r1 < D; ++r1) {           // out[b] = w[(b + r1) % d] for every row at once
+        const unsigned long long lo = rep * (unsigned long long)((1u << (D - r1)) - 1u);
+        planes[lane * D + r1] = ((x >> r1) & lo) | ((x << (D - r1)) & (kMaskDD ^ lo));
+      }
+    }
+  } else {
+    TabT* tab = reinterpret_cast<TabT*>(tab_raw);
+    if (lane < D) {
+      const TabT dv = (TabT)v | ((TabT)v << D), dp = (TabT)pl | ((TabT)pl << D);
+      const TabT dtv = (TabT)tv | ((TabT)tv << D), dtp = (TabT)tp | ((TabT)tp << D);
+      tab[0 * 2 * D + lane] = dv;
+      tab[0 * 2 * D + lane + D] = dv;
+      tab[1 * 2 * D + lane] = dp;
+      tab[1 * 2 * D + lane + D] = dp;
+      const int kv = (D - lane) % D, kp = D - 1 - lane;
+      tab[2 * 2 * D + kv] = dtv;
+      tab[2 * 2 * D + kv + D] = dtv;
+      tab[3 * 2 * D + kp] = dtp;
+      tab[3 * 2 * D + kp + D] = dtp;
+    }
+  }
+  __syncwarp();
+
+  // ---- bit stream -> output tiles -> TMA bulk stores ----
+  const int64_t f_start = off * (int64_t)(2 * DD);
+  // phantom elements in front (owned by the previous env; even): the stream starts at the kAlignBytes boundary
+  // below the env's first element, so every tile boundary after the first is aligned to it in global memory.
+  // Whole 128-byte lines per TMA store are worth +0.6 % (d=7) to +1.1 % (d=9) where the writer is HBM-bound
+  // (float32, d >= 6); where it is instruction-bound (small d, narrow elements) the up-to-31 extra phantom
+  // elements cost 1-2 %, so those keep the minimal 16-byte alignment (profiles/r01_writer_variants.txt).
+#ifdef TC_ALIGN_BYTES
+  constexpr int kAlignBytes = TC_ALIGN_BYTES;
+#else
+  constexpr int kAlignBytes = (OC::kB == 4 && D >= 6) ? 128 : 16;
+#endif
+  constexpr int kAlignElems = kAlignBytes / OC::kB;
+  static_assert(kAlignElems >= kE, "alignment below one 16-byte chunk");
+  constexpr int kShiftPlanes = (kAlignElems + DD - 1) / DD;   // empty planes in front so that gg below is >= 0
+  const int ph = (int)(f_start & (kAlignElems - 1));
+  const int phc = ph & ~(kE - 1);              // start of the 16-byte chunk holding the first own element
+  const int phr = ph - phc;                    // own elements start phr into that chunk (partial if != 0)
+  OutT* __restrict__ base = out + (f_start - ph);
+  const int F = P * 2 * DD;                    // >= 18 > kE, so head and tail chunks are never the same chunk
+  const int L = F + ph;
+  const int nW = (L + 31) >> 5;
+  const int nT = (L + kTileElems - 1) / kTileElems;
+  const int L16 = L & ~(kE - 1);               // elements covered by whole 16-byte chunks
+
+  auto assemble = [&](const int W) -> uint32_t {
+    uint32_t word = 0;
+    if (W < nW) {
+      if constexpr (Cfg::kPlane) {
+        const unsigned long long* planes = reinterpret_cast<const unsigned long long*>(tab_raw);
+        const int gg = 32 * W - ph + kShiftPlanes * DD;   // shifted by empty planes: never negative
+        const int kk = gg / DD;
+        const int r = gg - kk * DD;            // first stream bit of the word inside plane kk - kShiftPlanes
+#pragma unroll
+        for (int j = 0; j < Cfg::kPlanesPerWord; ++j) {
+          const int k = kk - kShiftPlanes + j;  // plane k = perspective k>>1, syndrome plane k&1
+          const int sh = j * DD - r;
+          if (k >= 0 && k < 2 * P && sh < 32) {
+            const unsigned long long pv = planes[(int)sp[k >> 1] + (k & 1) * DD];
+            word |= (j == 0) ? (uint32_t)(pv >> r) : ((uint32_t)pv << sh);
+          }
+        }
+      } else {
+        const TabT* tab = reinterpret_cast<const TabT*>(tab_raw);
+        const int tbit0 = 32 * W - ph;         // stream bit held by bit 0 of this word
+        const int tb = tbit0 < 0 ? 0 : tbit0;
+        const int f = tb / D;                  // first row field touching the word
+        int p = f / (2 * D);
+        int rr = f - p * (2 * D);              // c * D + a
+        int sh = f * D - tbit0;                // where that field starts inside the word (may be < 0)
+        uint32_t ent = sp[p];
+#pragma unroll
+        for (int it = 0; it < Cfg::kFields; ++it) {
+          if (sh < 32 && p < P) {
+            const int c = rr >= D ? 1 : 0;
+            const int a = rr - c * D;
+            const TabT tw = tab[(((ent & 1u) << 1) | c) * (2 * D) + a + ((ent >> 1) & 31u)];
+            const uint32_t fld = (uint32_t)(tw >> ((ent >> 6) & 31u)) & kRowMask;
+            word |= sh >= 0 ? (fld << sh) : (fld >> (-sh));
+          }
+          sh += D;
+          if (++rr == 2 * D) {
+            rr = 0;
+            ++p;
+            ent = sp[p];
+          }
+        }
+      }
+    }
+    return word;
+  };
+
+  // contiguous tile range per slice (measured: dealing the tiles round-robin to the slices is 15 % SLOWER than
+  // one warp per env at d=25, contiguous ranges are 10 % faster -- profiles/r01_writer_split_d25.txt)
+  const int t_begin = (int)((int64_t)nT * slice / split);
+  const int t_end = (int)((int64_t)nT * (slice + 1) / split);
+  for (int t = t_begin; t < t_end; ++t, ++ring) {
+    uint32_t word[kWordsPerLane];
+#pragma unroll
+    for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
+    OutT* st = stage + (ring % kStageBufs) * kTileElems;
+    if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
+      if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
+      __syncwarp();
+    }
+    uint4* st4 = reinterpret_cast<uint4*>(st);
+    constexpr int kSub = 32 / kE;              // 16-byte chunks per stream word (= lanes sharing a word)
+#pragma unroll
+    for (int u = 0; u < kWordsPerLane; ++u) {
+#pragma unroll
+      for (int s = 0; s < kSub; ++s) {         // 32 lanes x 16 bytes = 512 contiguous bytes per STS.128
+        const uint32_t wv = __shfl_sync(kFull, word[u], s * kE + lane / kSub);
+        st4[(u * kSub + s) * 32 + lane] = expand_chunk<OutT>(wv >> ((lane & (kSub - 1)) * kE), one16);
+      }
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    const int f0 = t * kTileElems;
+    // partial 16-byte chunks (shared with the neighbouring envs) go out as element pairs: head on lanes
+    // 0..kE/2-1, tail on lanes 8..8+kE/2-1
+    using PairT = typename OC::PairT;
+    if (t == 0 && phr && lane < kE / 2 && 2 * lane >= phr)
+      __stcs(reinterpret_cast<PairT*>(base + phc) + lane, reinterpret_cast<const PairT*>(st + phc)[lane]);
+    if (t == nT - 1 && lane >= 8 && 2 * (lane - 8) < L - L16)
+      __stcs(reinterpret_cast<PairT*>(base + L16) + (lane - 8),
+             reinterpret_cast<const PairT*>(st + (L16 - f0))[lane - 8]);
+    if (elect_one()) {
+      const int lo = t == 0 ? (phr ? phc + kE : phc) : 0;
+      int hi = L16 - f0;
+      if (hi > kTileElems) hi = kTileElems;
+      if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * OC::kB);
+      else asm volatile("cp.async.bulk.commit_group;" ::: "memory");     // keep one group per tile
+    }
+  }
+  __syncwarp();
+}
+
+template <int D, typename OutT>
+__global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
+persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
+                   const int64_t* __restrict__ block_off, int epb, OutT* __restrict__ out,
+                   uint8_t* __restrict__ pos, int64_t* __restrict__ offsets, int32_t* __restrict__ overflow,
+                   int64_t cap, int64_t n, uint32_t one16, int split) {
+  using Cfg = PerspCfg<D>;
+  constexpr uint32_t kFull = 0xffffffffu;
+  extern __shared__ __align__(128) unsigned char smem[];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const WriterCtx<D, OutT> cx(smem, warp, lane);
+  build_cand_table<D>(smem, Cfg::kWarps * 32);
   pdl_wait();                 // offsets / syndromes come from the kernels in front; the table above does not
   pdl_launch_dependents();
 
@@ -209,220 +463,7 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
       if (lane == 0 && overflow) *overflow = 1;
       continue;
     }
-    uint8_t* const pos_w = slice == 0 ? pos : nullptr;
-
-    // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
-    // One candidate qubit per lane and round; selected candidates are compacted in order with a ballot.
-    // sp[k]: plane path = index of the c=0 rolled plane of perspective k; row path = m | r0<<1 | r1<<6.
-    {
-      int kbase = 0;
-#pragma unroll 1
-      for (int q0 = 0; q0 < 2 * DD; q0 += 32) {
-        const int q = q0 + lane;
-        if constexpr (Cfg::kPlane) {
-          const uint2 cd = cand[q < 2 * DD ? q : 0];
-          const uint32_t r0m = __shfl_sync(kFull, m0, (cd.x >> 16) & 31u);
-          const uint32_t r1m = __shfl_sync(kFull, m1, (cd.x >> 16) & 31u);
-          const bool sel = q < 2 * DD && ((((cd.x >> 31) ? r1m : r0m) >> ((cd.x >> 24) & 31u)) & 1u);
-          const uint32_t bal = __ballot_sync(kFull, sel);
-          if (sel) {
-            const int k = kbase + __popc(bal & ((1u << lane) - 1u));
-            sp[k] = (uint16_t)cd.x;
-            if (pos_w) pos32[off + k] = cd.y;
-          }
-          kbase += __popc(bal);
-        } else {
-          const int m = q >= DD ? 1 : 0;
-          const int rem = q - m * DD;
-          const int i = rem / D, j = rem - i * D;
-          const uint32_t r0m = __shfl_sync(kFull, m0, i & 31), r1m = __shfl_sync(kFull, m1, i & 31);
-          const bool sel = q < 2 * DD && (((m ? r1m : r0m) >> j) & 1u);
-          const uint32_t bal = __ballot_sync(kFull, sel);
-          if (sel) {
-            const int k = kbase + __popc(bal & ((1u << lane) - 1u));
-            int ia = i - G; if (ia < 0) ia += D;
-            int rj = m ? G - j : j - G; if (rj < 0) rj += D;
-            const int r0 = m ? rj : ia, r1 = m ? ia : rj;
-            sp[k] = (uint16_t)(m | (r0 << 1) | (r1 << 6));
-            if (pos_w) pos32[off + k] = (uint32_t)m | ((uint32_t)i << 8) | ((uint32_t)j << 16);
-          }
-          kbase += __popc(bal);
-        }
-      }
-    }
-
-    // ---- base tables: t = 2m + c; row a of table t (see header) ----
-    uint32_t tv = 0, tp = 0;
-#pragma unroll
-    for (int b = 0; b < D; ++b) {
-      const uint32_t bv = __ballot_sync(kFull, (v >> b) & 1u);
-      const uint32_t bp = __ballot_sync(kFull, (pl >> b) & 1u);
-      if (lane == b) { tv = bv; tp = bp; }
-    }
-    if constexpr (Cfg::kPlane) {
-      unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw);
-      uint32_t* rows = reinterpret_cast<uint32_t*>(aux);                         // [4][16]: rows doubled
-      if (lane < D) {
-        const int kv = (D - lane) % D, kp = D - 1 - lane;
-        rows[0 * 16 + lane] = v;
-        rows[0 * 16 + lane + D] = v;
-        rows[1 * 16 + lane] = pl;
-        rows[1 * 16 + lane + D] = pl;
-        rows[2 * 16 + kv] = tv & kRowMask;
-        rows[2 * 16 + kv + D] = tv & kRowMask;
-        rows[3 * 16 + kp] = tp & kRowMask;
-        rows[3 * 16 + kp + D] = tp & kRowMask;
-      }
-      __syncwarp();
-      if (lane < 4 * D) {
-        // lane = t*d + r0: row-rolled plane x[a] = T[t][(a + r0) % d], then the d column rolls
-        const int t = lane / D, r0 = lane - t * D;
-        unsigned long long x = 0;
-#pragma unroll
-        for (int a = 0; a < D; ++a) x |= (unsigned long long)rows[t * 16 + a + r0] << (a * D);
-        constexpr unsigned long long kMaskDD = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
-        unsigned long long rep = 0;
-#pragma unroll
-        for (int a = 0; a < D; ++a) rep |= 1ull << (a * D);
-#pragma unroll
-        for (int r1 = 0; r1 < D; ++r1) {           // out[b] = w[(b + r1) % d] for every row at once
-          const unsigned long long lo = rep * (unsigned long long)((1u << (D - r1)) - 1u);
-          planes[lane * D + r1] = ((x >> r1) & lo) | ((x << (D - r1)) & (kMaskDD ^ lo));
-        }
-      }
-    } else {
-      TabT* tab = reinterpret_cast<TabT*>(tab_raw);
-      if (lane < D) {
-        const TabT dv = (TabT)v | ((TabT)v << D), dp = (TabT)pl | ((TabT)pl << D);
-        const TabT dtv = (TabT)tv | ((TabT)tv << D), dtp = (TabT)tp | ((TabT)tp << D);
-        tab[0 * 2 * D + lane] = dv;
-        tab[0 * 2 * D + lane + D] = dv;
-        tab[1 * 2 * D + lane] = dp;
-        tab[1 * 2 * D + lane + D] = dp;
-        const int kv = (D - lane) % D, kp = D - 1 - lane;
-        tab[2 * 2 * D + kv] = dtv;
-        tab[2 * 2 * D + kv + D] = dtv;
-        tab[3 * 2 * D + kp] = dtp;
-        tab[3 * 2 * D + kp + D] = dtp;
-      }
-    }
-    __syncwarp();
-
-    // ---- bit stream -> output tiles -> TMA bulk stores ----
-    const int64_t f_start = off * (int64_t)(2 * DD);
-    // phantom elements in front (owned by the previous env; even): the stream starts at the kAlignBytes boundary
-    // below the env's first element, so every tile boundary after the first is aligned to it in global memory.
-    // Whole 128-byte lines per TMA store are worth +0.6 % (d=7) to +1.1 % (d=9) where the writer is HBM-bound
-    // (float32, d >= 6); where it is instruction-bound (small d, narrow elements) the up-to-31 extra phantom
-    // elements cost 1-2 %, so those keep the minimal 16-byte alignment (profiles/r01_writer_variants.txt).
-#ifdef TC_ALIGN_BYTES
-    constexpr int kAlignBytes = TC_ALIGN_BYTES;
-#else
-    constexpr int kAlignBytes = (OC::kB == 4 && D >= 6) ? 128 : 16;
-#endif
-    constexpr int kAlignElems = kAlignBytes / OC::kB;
-    static_assert(kAlignElems >= kE, "alignment below one 16-byte chunk");
-    constexpr int kShiftPlanes = (kAlignElems + DD - 1) / DD;   // empty planes in front so that gg below is >= 0
-    const int ph = (int)(f_start & (kAlignElems - 1));
-    const int phc = ph & ~(kE - 1);              // start of the 16-byte chunk holding the first own element
-    const int phr = ph - phc;                    // own elements start phr into that chunk (partial if != 0)
-    OutT* __restrict__ base = out + (f_start - ph);
-    const int F = P * 2 * DD;                    // >= 18 > kE, so head and tail chunks are never the same chunk
-    const int L = F + ph;
-    const int nW = (L + 31) >> 5;
-    const int nT = (L + kTileElems - 1) / kTileElems;
-    const int L16 = L & ~(kE - 1);               // elements covered by whole 16-byte chunks
-
-    auto assemble = [&](const int W) -> uint32_t {
-      uint32_t word = 0;
-      if (W < nW) {
-        if constexpr (Cfg::kPlane) {
-          const unsigned long long* planes = reinterpret_cast<const unsigned long long*>(tab_raw);
-          const int gg = 32 * W - ph + kShiftPlanes * DD;   // shifted by empty planes: never negative
-          const int kk = gg / DD;
-          const int r = gg - kk * DD;            // first stream bit of the word inside plane kk - kShiftPlanes
-#pragma unroll
-          for (int j = 0; j < Cfg::kPlanesPerWord; ++j) {
-            const int k = kk - kShiftPlanes + j;  // plane k = perspective k>>1, syndrome plane k&1
-            const int sh = j * DD - r;
-            if (k >= 0 && k < 2 * P && sh < 32) {
-              const unsigned long long pv = planes[(int)sp[k >> 1] + (k & 1) * DD];
-              word |= (j == 0) ? (uint32_t)(pv >> r) : ((uint32_t)pv << sh);
-            }
-          }
-        } else {
-          const TabT* tab = reinterpret_cast<const TabT*>(tab_raw);
-          const int tbit0 = 32 * W - ph;         // stream bit held by bit 0 of this word
-          const int tb = tbit0 < 0 ? 0 : tbit0;
-          const int f = tb / D;                  // first row field touching the word
-          int p = f / (2 * D);
-          int rr = f - p * (2 * D);              // c * D + a
-          int sh = f * D - tbit0;                // where that field starts inside the word (may be < 0)
-          uint32_t ent = sp[p];
-#pragma unroll
-          for (int it = 0; it < Cfg::kFields; ++it) {
-            if (sh < 32 && p < P) {
-              const int c = rr >= D ? 1 : 0;
-              const int a = rr - c * D;
-              const TabT tw = tab[(((ent & 1u) << 1) | c) * (2 * D) + a + ((ent >> 1) & 31u)];
-              const uint32_t fld = (uint32_t)(tw >> ((ent >> 6) & 31u)) & kRowMask;
-              word |= sh >= 0 ? (fld << sh) : (fld >> (-sh));
-            }
-            sh += D;
-            if (++rr == 2 * D) {
-              rr = 0;
-              ++p;
-              ent = sp[p];
-            }
-          }
-        }
-      }
-      return word;
-    };
-
-    // contiguous tile range per slice (measured: dealing the tiles round-robin to the slices is 15 % SLOWER than
-    // one warp per env at d=25, contiguous ranges are 10 % faster -- profiles/r01_writer_split_d25.txt)
-    const int t_begin = (int)((int64_t)nT * slice / split);
-    const int t_end = (int)((int64_t)nT * (slice + 1) / split);
-    for (int t = t_begin; t < t_end; ++t, ++ring) {
-      uint32_t word[kWordsPerLane];
-#pragma unroll
-      for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
-      OutT* st = stage + (ring % kStageBufs) * kTileElems;
-      if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
-        if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
-        __syncwarp();
-      }
-      uint4* st4 = reinterpret_cast<uint4*>(st);
-      constexpr int kSub = 32 / kE;              // 16-byte chunks per stream word (= lanes sharing a word)
-#pragma unroll
-      for (int u = 0; u < kWordsPerLane; ++u) {
-#pragma unroll
-        for (int s = 0; s < kSub; ++s) {         // 32 lanes x 16 bytes = 512 contiguous bytes per STS.128
-          const uint32_t wv = __shfl_sync(kFull, word[u], s * kE + lane / kSub);
-          st4[(u * kSub + s) * 32 + lane] = expand_chunk<OutT>(wv >> ((lane & (kSub - 1)) * kE), one16);
-        }
-      }
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      __syncwarp();
-      const int f0 = t * kTileElems;
-      // partial 16-byte chunks (shared with the neighbouring envs) go out as element pairs: head on lanes
-      // 0..kE/2-1, tail on lanes 8..8+kE/2-1
-      using PairT = typename OC::PairT;
-      if (t == 0 && phr && lane < kE / 2 && 2 * lane >= phr)
-        __stcs(reinterpret_cast<PairT*>(base + phc) + lane, reinterpret_cast<const PairT*>(st + phc)[lane]);
-      if (t == nT - 1 && lane >= 8 && 2 * (lane - 8) < L - L16)
-        __stcs(reinterpret_cast<PairT*>(base + L16) + (lane - 8),
-               reinterpret_cast<const PairT*>(st + (L16 - f0))[lane - 8]);
-      if (elect_one()) {
-        const int lo = t == 0 ? (phr ? phc + kE : phc) : 0;
-        int hi = L16 - f0;
-        if (hi > kTileElems) hi = kTileElems;
-        if (hi > lo) bulk_store(base + f0 + lo, st + lo, (hi - lo) * OC::kB);
-        else asm volatile("cp.async.bulk.commit_group;" ::: "memory");     // keep one group per tile
-      }
-    }
-    __syncwarp();
+    write_env<D, OutT>(cx, v, pl, m0, m1, P, off, slice, split, ring, out, slice == 0 ? pos : nullptr, one16);
   }
   __syncwarp();
   // the staging tiles must stay valid until the TMA engine has READ them; the global writes themselves complete

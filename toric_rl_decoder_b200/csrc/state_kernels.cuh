@@ -87,97 +87,7 @@ __device__ __forceinline__ bool parity_even(uint32_t gmask, const Rows& s) {
   return gxor<G>(gmask, par) == 0;
 }
 
-struct SampleStats {
-  int attempts;
-  int nx, ny, nz;
-};
-
-// ToricCode.reset's sampling loop (ToricCode.py:108-117): draw errors until the syndrome is non-trivial.
-// Draw numbering (the oracle restates exactly this; see DESIGN.md "RNG"):
-//   depolarizing: attempt a, matrix m, row i, column pair k -> Philox counter word3 = a<<10 | m<<9 | i<<4 | k;
-//                 output words (u0, c0, u1, c1) serve columns 2k and 2k+1: error iff u < p_thresh,
-//                 Pauli code 1 + mulhi(c, 3)                                  (ToricCode.py:141-149)
-//   fixed-weight: draw t of attempt a -> word3 = kDomFixed | (a & 1023)<<20 | (t & 0xfffff);
-//                 qubit index = u0 & (pow2 - 1), rejected when >= 2d^2 or already occupied; code as above
-//                                                                            (ToricCode.py:159-164)
-template <int G>
-__device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint64_t env_id, uint32_t episode,
-                                              uint32_t thresh, int mode, int n_fixed, uint2 key, Rows& s,
-                                              uint8_t& status, SampleStats& st) {
-  const bool one_draw = (mode & kSampleOneDraw) != 0;   // the bare generators: no non-trivial-syndrome rejection
-  mode &= 3;
-  const int nq = 2 * d * d;
-  const int nf = n_fixed < nq ? n_fixed : nq;
-  uint32_t pm = 1;
-  while ((int)pm < nq) pm <<= 1;
-  pm -= 1;
-  const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
-  const uint32_t cap = (mode == 0) ? kMaxAttempts : kMaxFixedAttempts;
-  uint32_t attempt = 0;
-  while (true) {
-    s.x0 = s.x1 = s.z0 = s.z1 = 0;
-    if (mode != 0) {
-      int placed = 0;
-      uint32_t t = 0;
-      while (placed < nf) {
-        const uint4 rnd = philox4x32_10(
-            make_uint4(elo, ehi, episode, kDomFixed | ((attempt & 1023u) << 20) | (t & 0xfffffu)), key);
-        ++t;
-        const int q = (int)(rnd.x & pm);
-        if (q >= nq) continue;
-        const int m = q / (d * d);
-        const int rem = q - m * d * d;
-        const int i = rem / d;
-        const int j = rem - i * d;
-        const uint32_t mine = ((m == 0 ? (s.x0 | s.z0) : (s.x1 | s.z1)) >> j) & 1u;
-        if (gshfl<G>(gmask, mine, i)) continue;
-        const uint32_t code = 1u + mulhi32(rnd.y, 3u);
-        if (r == i) {
-          const uint32_t bit = 1u << j;
-          const uint32_t xb = (code == 1u || code == 2u) ? bit : 0u;
-          const uint32_t zb = (code >= 2u) ? bit : 0u;
-          if (m == 0) { s.x0 |= xb; s.z0 |= zb; } else { s.x1 |= xb; s.z1 |= zb; }
-        }
-        ++placed;
-      }
-    }
-    if (mode != 1 && r < d) {
-      const uint32_t occ0 = s.x0 | s.z0, occ1 = s.x1 | s.z1;
-      const int pairs = (d + 1) >> 1;
-#pragma unroll 1
-      for (int m = 0; m < 2; ++m) {
-        const uint32_t occ = m ? occ1 : occ0;
-        uint32_t xr = 0, zr = 0;
-        for (int k = 0; k < pairs; ++k) {
-          const uint4 rnd = philox4x32_10(
-              make_uint4(elo, ehi, episode, (attempt << 10) | ((uint32_t)m << 9) | ((uint32_t)r << 4) | (uint32_t)k),
-              key);
-          const int j0 = 2 * k, j1 = 2 * k + 1;
-          if (rnd.x < thresh && !((occ >> j0) & 1u)) {
-            const uint32_t code = 1u + mulhi32(rnd.y, 3u);
-            if (code <= 2u) xr |= 1u << j0;
-            if (code >= 2u) zr |= 1u << j0;
-          }
-          if (j1 < d && rnd.z < thresh && !((occ >> j1) & 1u)) {
-            const uint32_t code = 1u + mulhi32(rnd.w, 3u);
-            if (code <= 2u) xr |= 1u << j1;
-            if (code >= 2u) zr |= 1u << j1;
-          }
-        }
-        if (m == 0) { s.x0 |= xr; s.z0 |= zr; } else { s.x1 |= xr; s.z1 |= zr; }
-      }
-    }
-    syndrome_rows<G>(gmask, d, r, s);
-    const uint32_t any = __ballot_sync(gmask, (s.v | s.pl) != 0u) & gmask;
-    ++attempt;
-    if (any || one_draw) break;
-    if (attempt >= cap) { status |= kStatusResetGaveUp; break; }
-  }
-  st.attempts = (int)attempt;
-  st.nx = __popc(s.x0 & ~s.z0) + __popc(s.x1 & ~s.z1);
-  st.ny = __popc(s.x0 & s.z0) + __popc(s.x1 & s.z1);
-  st.nz = __popc(s.z0 & ~s.x0) + __popc(s.z1 & ~s.x1);
-}
+// K1 sampler (sample_errors, SampleStats): sampler.cuh, included at the end of this file
 
 // position of the n-th (0-based) set bit of m; m must have more than n bits set
 __device__ __forceinline__ int nth_set_bit(uint32_t m, int n) {
@@ -223,3 +133,5 @@ __device__ __forceinline__ void random_action(uint32_t gmask, int d, int r, uint
 }
 
 }  // namespace tc
+
+#include "sampler.cuh"

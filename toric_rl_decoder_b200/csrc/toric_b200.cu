@@ -2,7 +2,10 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
 #include "../../include/toric_b200.h"
 
+#include <mutex>
+
 #include "common.cuh"
+#include "fused_step.cuh"
 #include "persp_write.cuh"
 #include "policy_kernels.cuh"
 #include "state_kernels.cuh"
@@ -331,27 +334,7 @@ scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ 
 // fused actor iteration: [random action] -> step -> reward/terminal -> bookkeeping / auto-reset -> count
 // (loop body of src/Actor_mp.py:104-185 without the network; perspectives follow in persp_write_kernel)
 // ------------------------------------------------------------------------------------------------
-struct ActorArgs {
-  uint32_t* qubits;
-  uint32_t* syn;
-  uint32_t* prev_syn;
-  int32_t* actions;
-  float* reward;
-  uint8_t* terminal;
-  uint8_t* gs;
-  uint8_t* status;
-  int32_t* steps;
-  uint32_t* episode;
-  const uint32_t* p_thresh;
-  int64_t* counters;
-  int32_t* counts;
-  int32_t* local_off;
-  int32_t* block_sum;
-  uint2 key;
-  int64_t env_base;
-  int64_t n;
-  int flags, max_steps, mode, n_fixed, d;
-};
+// ActorArgs: fused_step.cuh
 
 #ifndef TC_ACTOR_MIN_CTAS
 #define TC_ACTOR_MIN_CTAS 5   /* 48 registers: 5 CTAs per SM, 2048 CTAs at 65536 envs = 2.8 waves instead of 3.5 */
@@ -491,6 +474,7 @@ struct Workspace {
   int64_t* block_off;
   int64_t nblocks;
   int epb;
+  ScanWs scan;        // single-pass step: launch counter + look-back descriptors (never touched by the other kernels)
   size_t bytes;
 };
 
@@ -507,6 +491,13 @@ inline Workspace carve(void* ws, int d, int64_t n) {
   o = (o + 15) & ~(size_t)15;
   w.block_off = reinterpret_cast<int64_t*>(base + o);
   o += (size_t)w.nblocks * 8;
+  o = (o + 127) & ~(size_t)127;
+  w.scan.header = reinterpret_cast<uint32_t*>(base + o);
+  o += 64;
+  w.scan.desc1 = reinterpret_cast<unsigned long long*>(base + o);
+  o += (size_t)((n + 31) / 32) * 8;
+  w.scan.desc0 = reinterpret_cast<uint32_t*>(base + o);
+  o += (size_t)n * 4;
   w.bytes = (o + 255) & ~(size_t)255;
   return w;
 }
@@ -517,18 +508,20 @@ int launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* po
                   int32_t* overflow, int64_t cap, int64_t n, uint32_t one16, cudaStream_t st) {
   using Cfg = PerspCfg<D>;
   constexpr int WPB = Cfg::kWarps;
-  static int slots[64] = {0};                     // per device: SMs x resident CTAs of this instantiation
+  // per device and instantiation, once (thread-safe): opt in to the dynamic shared memory, SMs x resident CTAs
+  static int slots[64] = {0};
+  static std::once_flag once[64];
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (slots[dev] == 0) {
+  std::call_once(once[dev], [dev] {
     cudaFuncSetAttribute(persp_write_kernel<D, OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          Cfg::kSmemBytes);
     int sms = 148, occ = 1;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, persp_write_kernel<D, OutT>, WPB * 32, Cfg::kSmemBytes);
     slots[dev] = sms * (occ > 0 ? occ : 1);
-  }
+  });
   // TC_WRITE_WAVES: CTAs per resident slot.  0 = one env per warp (the hardware CTA scheduler staggers the
   // env setups against the streaming of the others); k > 0 = persistent warps walking ~n/(slots*k*WPB) envs.
 #ifndef TC_WRITE_WAVES
@@ -572,6 +565,38 @@ int write_dispatch(int d, const uint32_t* syn, const Workspace& w, OutT* out, ui
     TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16) TC_CASE(17) TC_CASE(18)
     TC_CASE(19) TC_CASE(20) TC_CASE(21) TC_CASE(22) TC_CASE(23) TC_CASE(24) TC_CASE(25) TC_CASE(26)
     TC_CASE(27) TC_CASE(28) TC_CASE(29) TC_CASE(30) TC_CASE(31) TC_CASE(32)
+#undef TC_CASE
+    default: return -1;
+  }
+  return launch_status();
+}
+
+// single-pass step (fused_step.cuh): one env per warp, CTAs in env order
+template <int D>
+int launch_fused(const ActorArgs& a, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
+                 int32_t* overflow, int64_t cap, cudaStream_t st) {
+  using Cfg = PerspCfg<D>;
+  static std::once_flag once[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  std::call_once(once[dev], [] {
+    cudaFuncSetAttribute(fused_step_kernel<D, float>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  launch_pdl(fused_step_kernel<D, float>, grid_for(a.n, Cfg::kWarps), Cfg::kWarps * 32, Cfg::kSmemBytes, st, a,
+             w.scan, out, pos, offsets, overflow, cap, 0u);
+  return 0;
+}
+
+int fused_dispatch(const ActorArgs& a, const Workspace& w, float* out, uint8_t* pos, int64_t* offsets,
+                   int32_t* overflow, int64_t cap, cudaStream_t st) {
+  switch (a.d) {
+#define TC_CASE(D) \
+  case D:          \
+    launch_fused<D>(a, w, out, pos, offsets, overflow, cap, st); \
+    break;
+    TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8) TC_CASE(9) TC_CASE(10)
+    TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16)
 #undef TC_CASE
     default: return -1;
   }
@@ -778,6 +803,28 @@ int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* 
                   uint64_t seed, int64_t env_base, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
                   int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d, int64_t n,
                   void* stream) {
+  if (flags & TC_ACTOR_SINGLE_PASS) {
+    if (bad_d(d) || d > TC_SINGLE_PASS_MAX_D || n < 0 || cap < 0 || !offsets) return -1;
+    if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+      cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+      return launch_status();
+    }
+    if (!qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode || !p_thresh || !counts ||
+        !workspace || (cap > 0 && !out))
+      return -1;
+    if (((uintptr_t)actions & 15) || ((uintptr_t)out & 15) || ((uintptr_t)pos & 3)) return -1;
+    const Workspace w = carve(workspace, d, n);
+    if (workspace_bytes < w.bytes) return -2;
+    ActorArgs a;
+    a.qubits = qubits; a.syn = syn; a.prev_syn = prev_syn; a.actions = actions; a.reward = reward;
+    a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
+    a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
+    a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
+    a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d;
+    return fused_dispatch(a, w, out, pos, offsets, overflow, cap, st);
+  }
   const int rc = tc_actor_pre(qubits, syn, prev_syn, actions, reward, terminal, gs, status, steps, episode,
                               p_thresh, counters, flags, max_steps, mode, n_fixed, seed, env_base, counts, offsets,
                               workspace, workspace_bytes, d, n, stream);

@@ -19,6 +19,8 @@ SAMPLE_ONE_DRAW = 16      # OR-ed into the mode: one generator draw, no rejectio
 ACTOR_RANDOM_ACTIONS = 1
 ACTOR_AUTO_RESET = 2
 ACTOR_FREEZE_DONE = 4
+ACTOR_SINGLE_PASS = 8     # one kernel per step (step + look-back scan + writer) instead of three; d <= 16, float32
+SINGLE_PASS_MAX_D = 16
 
 STATUS_BAD_ACTION = 1
 STATUS_RESET_GAVE_UP = 2
@@ -58,13 +60,17 @@ class ToricEngine:
     """
 
     def __init__(self, d, n, device="cuda", seed=0, env_base=0, p_error=0.1, max_steps=75,
-                 out_dtype=torch.float32):
+                 out_dtype=torch.float32, single_pass=False):
         """out_dtype: element type of the perspective tensor -- float32 (the reference's,
-        src/numba/util_actor.py:39), or bfloat16 / float16 / uint8 (same 0/1 values, 2-4x less HBM traffic)."""
+        src/numba/util_actor.py:39), or bfloat16 / float16 / uint8 (same 0/1 values, 2-4x less HBM traffic).
+        single_pass: actor_step() issues the one-kernel form of the step (TC_ACTOR_SINGLE_PASS: step, cross-env
+        scan by decoupled look-back and perspective writer fused) where it applies (d <= 16, float32, no
+        `between` hook); results are identical bit for bit."""
         self.lib = _lib.load()
         if out_dtype not in OUT_DTYPES:
             raise ValueError("out_dtype must be one of %s" % (sorted(str(k) for k in OUT_DTYPES),))
         self.out_dtype = out_dtype
+        self.single_pass = bool(single_pass)
         if not (3 <= int(d) <= 32):
             raise ValueError("lattice size d must be in [3, 32]")
         if not torch.cuda.is_available():
@@ -79,7 +85,8 @@ class ToricEngine:
         self.qubits = z((n_, 4, d_), torch.int32)
         self.syn = z((n_, 2, d_), torch.int32)
         self.prev_syn = None
-        self.gs = torch.ones(n_, dtype=torch.uint8, device=dev)
+        self.gs = torch.ones(n_, dtype=torch.uint8, device=dev)        # sticky flag of evalGroundState (tc_ground_state)
+        self.step_gs = torch.ones(n_, dtype=torch.uint8, device=dev)   # per-step parity result of the fused actor step
         self.status = z(n_, torch.uint8)
         self.steps = z(n_, torch.int32)
         self.episode = z(n_, torch.int32)
@@ -238,7 +245,7 @@ class ToricEngine:
         if self.out_dtype is not torch.float32 or between is not None:   # the fused entry point's two halves
             _lib.check(self.lib.tc_actor_pre(
                 _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
-                _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+                _ptr(reward), _ptr(terminal), _ptr(self.step_gs), _ptr(self.status), _ptr(self.steps),
                 _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
                 int(n_fixed), self.seed, self.env_base, _ptr(counts), _ptr(self.offsets), _ptr(self.workspace),
                 self.workspace.numel(), self.d, self.n, _stream(self.device)), "tc_actor_pre")
@@ -246,9 +253,11 @@ class ToricEngine:
                 between()
             self.persp_write()
             return
+        if self.single_pass and self.d <= SINGLE_PASS_MAX_D:
+            flags |= ACTOR_SINGLE_PASS
         _lib.check(self.lib.tc_actor_step(
             _ptr(self.qubits), _ptr(self.syn), _ptr(self.prev_syn if keep_prev else None), _ptr(act_buf),
-            _ptr(reward), _ptr(terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps),
+            _ptr(reward), _ptr(terminal), _ptr(self.step_gs), _ptr(self.status), _ptr(self.steps),
             _ptr(self.episode), _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode),
             int(n_fixed), self.seed, self.env_base, _ptr(self.out), _ptr(self.pos), _ptr(counts),
             _ptr(self.offsets), _ptr(self.overflow), self.cap, _ptr(self.workspace), self.workspace.numel(),
@@ -284,7 +293,7 @@ class ToricEngine:
         self._last_syn = self.syn
         _lib.check(self.lib.tc_actor_pre(
             _ptr(self.qubits), _ptr(self.syn), _ptr(None), _ptr(self.actions), _ptr(self.reward),
-            _ptr(self.terminal), _ptr(self.gs), _ptr(self.status), _ptr(self.steps), _ptr(self.episode),
+            _ptr(self.terminal), _ptr(self.step_gs), _ptr(self.status), _ptr(self.steps), _ptr(self.episode),
             _ptr(self.p_thresh), _ptr(self.counters), flags, self.max_steps, int(mode), int(n_fixed), self.seed,
             self.env_base, _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace), self.workspace.numel(),
             self.d, self.n, _stream(self.device)), "tc_actor_pre")

@@ -28,6 +28,8 @@ _engines = {}
 
 
 def _engine(d, n, device):
+    """Scratch engine per (d, device): only its workspace / counts / offsets are used here (a few bytes per env);
+    the perspective tensors handed to callers are allocated per call."""
     key = (d, str(device))
     eng = _engines.get(key)
     if eng is None or eng.n < n:
@@ -39,20 +41,34 @@ def _engine(d, n, device):
 def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda", raw_positions=False):
     """states: (N,2,d,d) array/tensor of 0/1.  Returns (perspectives f32 (sumP,2,d,d) cuda tensor,
     positions int64 (sumP,3) cuda tensor, counts int32 (N,), offsets int64 (N+1,)).  raw_positions=True keeps
-    the positions as the device layout uint8 (sumP,4) = (m,i,j,0) that tc_select_action consumes."""
+    the positions as the device layout uint8 (sumP,4) = (m,i,j,0) that tc_select_action consumes.
+
+    Like the reference (src/numba/util_actor.py:56-67 returns fresh lists) every call returns FRESH tensors
+    sized to sumP: count + scan first, then one allocation, then the writer -- a later call (perspectives of
+    `next_state` after `state`, target network after policy network) never overwrites an earlier result."""
+    from . import _lib
+    from .engine import OUT_DTYPES, _ptr, _stream
     d = int(toric_size)
     if int(grid_shift) != d // 2:
         raise ValueError("grid_shift must be toric_size // 2 (src/Actor_mp.py:59)")
     st = torch.as_tensor(np.ascontiguousarray(states) if isinstance(states, np.ndarray) else states)
     n = st.shape[0]
     eng = _engine(d, n, device)
-    syn = torch.zeros((n, 2, d), dtype=torch.int32, device=eng.device)
-    u8 = (st != 0).to(device=eng.device, dtype=torch.uint8).contiguous()
-    from . import _lib
-    from .engine import _ptr, _stream
-    _lib.check(eng.lib.tc_pack_state(_ptr(u8), _ptr(syn), d, n, _stream()), "tc_pack_state")
-    eng.perspectives(syn=syn, n=n)
-    persp, pos, counts, offsets = eng.perspective_views(n)
+    dev = eng.device
+    syn = torch.zeros((n, 2, d), dtype=torch.int32, device=dev)
+    u8 = (st != 0).to(device=dev, dtype=torch.uint8).contiguous()
+    with torch.cuda.device(dev):
+        _lib.check(eng.lib.tc_pack_state(_ptr(u8), _ptr(syn), d, n, _stream(dev)), "tc_pack_state")
+        eng.perspectives_count(syn=syn, n=n)
+        total = eng.total_perspectives(n)                       # one 8-byte host read
+        persp = torch.empty((total, 2, d, d), dtype=torch.float32, device=dev)
+        pos = torch.empty((total, 4), dtype=torch.uint8, device=dev)
+        overflow = torch.zeros(1, dtype=torch.int32, device=dev)
+        if n > 0:
+            _lib.check(eng.lib.tc_persp_write_as(_ptr(syn), _ptr(persp), OUT_DTYPES[torch.float32], _ptr(pos),
+                                                 _ptr(eng.offsets), _ptr(overflow), total, _ptr(eng.workspace),
+                                                 eng.workspace.numel(), d, n, _stream(dev)), "tc_persp_write_as")
+        counts, offsets = eng.counts[:n].clone(), eng.offsets[:n + 1].clone()
     if raw_positions:
         return persp, pos, counts, offsets
     return persp, pos[:, :3].to(torch.int64), counts, offsets
