@@ -82,7 +82,8 @@ def check_first_error_position(q, p, bins=14, what="first error"):
     pk = (1 - p) ** k * p / (1 - (1 - p) ** nq)
     groups = [list(g) for g in np.array_split(k, bins)]
     while len(groups) > 2 and n * pk[groups[-1]].sum() < 20:       # merge the thin tail (large p: K is small)
-        groups[-2] += groups.pop()
+        tail = groups.pop()
+        groups[-1] = groups[-1] + tail
     obs = [float(np.isin(first, g).sum()) for g in groups]
     exp = [n * pk[g].sum() for g in groups]
     _chi2_ok(obs, exp, what)
