@@ -395,6 +395,60 @@ def test_single_pass_step_equals_three_kernel_step(pkg, d, n, steps):
     assert a.read_counters()["episodes"] > 0 or n < 10
 
 
+@pytest.mark.parametrize("d,n,steps,single_pass", ((7, 1500, 400, False), (7, 40000, 120, False), (5, 300, 400, False),
+                                                   (7, 1500, 400, True), (7, 40000, 120, True), (9, 700, 200, True)))
+def test_pdl_chain_matches_serialized_launches(pkg, d, n, steps, single_pass):
+    """Programmatic dependent launch (csrc/common.cuh: no exit path before pdl_wait) must not change results: long
+    chains of back-to-back fused steps -- small batches, where a kernel's CTAs really are resident while the previous
+    kernel drains -- against the TC_PDL=0 build of the same sources, where every launch takes a full dependency."""
+    import os
+    from toric_rl_decoder_b200 import _lib, buildlib
+    if not os.path.exists(buildlib.NOPDL_LIB_PATH):
+        pytest.skip("libtoric_b200_nopdl.so not built (__graft_entry__.build() makes it)")
+    a = pkg.ToricEngine(d, n, seed=21, p_error=0.1, max_steps=12, single_pass=single_pass)
+    b = pkg.ToricEngine(d, n, seed=21, p_error=0.1, max_steps=12, single_pass=single_pass)
+    b.lib = _lib.bind(buildlib.NOPDL_LIB_PATH)
+    for e in (a, b):
+        e.reset()
+    sums_a, sums_b = [], []
+    for t in range(steps):
+        a.actor_step()
+        sums_a.append(a.out[:1024].sum() + a.offsets[n])        # reads behind the writer, enqueued in the chain
+    for t in range(steps):
+        b.actor_step()
+        sums_b.append(b.out[:1024].sum() + b.offsets[n])
+    torch.cuda.synchronize()
+    assert torch.equal(torch.stack(sums_a), torch.stack(sums_b))
+    for name in ("qubits", "syn", "steps", "episode", "counters", "counts", "offsets", "reward", "terminal"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    for x, y in zip(a.perspective_views(), b.perspective_views()):
+        assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("single_pass", (False, True))
+def test_state_dict_exact_resume(pkg, tmp_path, single_pass):
+    """run k steps, save, run k more == load into a fresh engine (through torch.save / torch.load), run k more."""
+    d, n, k = 7, 5000, 40
+    a = pkg.ToricEngine(d, n, seed=77, env_base=123456, p_error=0.07, max_steps=9, single_pass=single_pass)
+    a.reset()
+    for _ in range(k):
+        a.actor_step(keep_prev=True)
+    torch.save(a.state_dict(), tmp_path / "engine.pt")
+    for _ in range(k):
+        a.actor_step(keep_prev=True)
+    b = pkg.ToricEngine(d, n, seed=0, env_base=0, p_error=0.5, max_steps=3, single_pass=single_pass)   # all overwritten
+    b.load_state_dict(torch.load(tmp_path / "engine.pt"))
+    for _ in range(k):
+        b.actor_step(keep_prev=True)
+    for name in pkg.ToricEngine._STATE_TENSORS + ("prev_syn", "counts", "offsets"):
+        assert torch.equal(getattr(a, name), getattr(b, name)), name
+    for x, y in zip(a.perspective_views(), b.perspective_views()):
+        assert torch.equal(x, y)
+    assert a.read_counters() == b.read_counters() and a.read_counters()["episodes"] > 0
+    with pytest.raises(ValueError):
+        pkg.ToricEngine(5, n).load_state_dict(a.state_dict())
+
+
 def test_single_pass_step_capacity_overflow_flag(pkg):
     eng = pkg.ToricEngine(7, 500, seed=1, p_error=0.1, single_pass=True)
     eng.reset()

@@ -43,6 +43,19 @@ ABI_VERSION = 4
 _lib = None
 
 
+def bind(path):
+    """ctypes handle of one build of the library with every prototype set (a second build of the same sources,
+    e.g. the TC_PDL=0 variant the dependent-launch stress test compares against, can be bound next to the default)."""
+    lib = ctypes.CDLL(path)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)      # AttributeError if the symbol is missing
+        fn.argtypes = argtypes
+        fn.restype = _i
+    if lib.tc_abi_version() != ABI_VERSION:
+        raise RuntimeError("%s: ABI version mismatch" % path)
+    return lib
+
+
 def load():
     """Load the shared library (once).  Raises if it has not been built."""
     global _lib
@@ -52,15 +65,8 @@ def load():
         raise RuntimeError(
             "libtoric_b200.so is not built (%s). Run `python -m toric_rl_decoder_b200.buildlib` or "
             "`__graft_entry__.build()`. There is no CPU fallback." % LIB_PATH)
-    lib = ctypes.CDLL(LIB_PATH)
-    for name, argtypes in SIGNATURES.items():
-        fn = getattr(lib, name)      # AttributeError if the symbol is missing
-        fn.argtypes = argtypes
-        fn.restype = _i
-    if lib.tc_abi_version() != ABI_VERSION:
-        raise RuntimeError("libtoric_b200.so ABI version mismatch")
-    _lib = lib
-    return lib
+    _lib = bind(LIB_PATH)
+    return _lib
 
 
 def check(rc, what):

@@ -19,6 +19,15 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
               "-shared", "-Xcompiler", "-fPIC", "-diag-suppress", "63"]
 
 
+# the same sources with programmatic dependent launch compiled out (every launch takes a full stream dependency):
+# the reference build tests/test_gpu_actor.py::test_pdl_chain_matches_serialized_launches compares long chains with
+NOPDL_LIB_PATH = os.path.join(PKG_DIR, "libtoric_b200_nopdl.so")
+
+
+def build_nopdl():
+    return build(defines=("TC_PDL=0",), out=NOPDL_LIB_PATH)
+
+
 def is_stale():
     if not os.path.exists(LIB_PATH):
         return True

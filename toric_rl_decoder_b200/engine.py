@@ -38,6 +38,25 @@ def p_to_thresh(p):
     return np.minimum(np.floor(p * 4294967296.0), 4294967295.0).astype(np.uint32)
 
 
+class _Range:
+    """NVTX range per phase (reset / step / perspectives / actor_step ...), visible in nsys / ncu timelines; the
+    push/pop pair costs well under a microsecond when no profiler is attached.  ToricEngine.nvtx = False disables it."""
+    __slots__ = ("on",)
+
+    def __init__(self, name, on=True):
+        self.on = on
+        if on:
+            torch.cuda.nvtx.range_push(name)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        if self.on:
+            torch.cuda.nvtx.range_pop()
+        return False
+
+
 def _ptr(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
 
@@ -58,6 +77,12 @@ class ToricEngine:
     Device layout (include/toric_b200.h): qubits int32[n,4,d] (bit planes x0,x1,z0,z1, one row per word),
     syn int32[n,2,d] (vertex, plaquette planes).
     """
+
+    nvtx = True        # NVTX ranges "toric/<phase>" around every enqueue (class-wide switch)
+    # what state_dict() saves: with the counter-based sampler (Philox keyed by seed, global env id, episode, step)
+    # these tensors + the scalars below are the WHOLE state of the env batch, so a resumed run is bit-identical
+    _STATE_TENSORS = ("qubits", "syn", "gs", "step_gs", "status", "steps", "episode", "p_thresh", "counters",
+                      "actions", "reward", "terminal")
 
     def __init__(self, d, n, device="cuda", seed=0, env_base=0, p_error=0.1, max_steps=75,
                  out_dtype=torch.float32, single_pass=False):
@@ -163,6 +188,10 @@ class ToricEngine:
 
     # -- kernels ---------------------------------------------------------------------------------
     def syndrome(self):
+        with _Range("toric/syndrome", self.nvtx):
+            self._syndrome()
+
+    def _syndrome(self):
         _lib.check(self.lib.tc_syndrome(_ptr(self.qubits), _ptr(self.syn), self.d, self.n, _stream(self.device)), "tc_syndrome")
 
     def reset(self, idx=None, mode=SAMPLE_DEPOLARIZING, n_fixed=0):
@@ -173,9 +202,11 @@ class ToricEngine:
             idx_t = torch.as_tensor(idx, dtype=torch.int64, device=self.device).contiguous()
             n_idx = idx_t.numel()
             self.steps[idx_t] = 0
+        rng = _Range("toric/reset", self.nvtx)
         _lib.check(self.lib.tc_reset(_ptr(self.qubits), _ptr(self.syn), _ptr(self.gs), _ptr(self.status),
                                      _ptr(self.p_thresh), _ptr(self.episode), _ptr(idx_t), n_idx, int(mode),
                                      int(n_fixed), self.seed, self.env_base, self.d, _stream(self.device)), "tc_reset")
+        rng.__exit__()
         if idx is None:
             self.steps.zero_()
 
@@ -184,10 +215,12 @@ class ToricEngine:
         a = torch.as_tensor(actions)
         if tuple(a.shape) != (self.n, 4):
             raise ValueError("actions must have shape (%d, 4)" % self.n)
-        self.actions.copy_(a.to(torch.int32), non_blocking=True)
-        _lib.check(self.lib.tc_step(_ptr(self.qubits), _ptr(self.syn), _ptr(self.actions), _ptr(self.reward),
-                                    _ptr(self.terminal), _ptr(self.status), self.d, self.n, _stream(self.device)), "tc_step")
-        self.steps += 1
+        with _Range("toric/step", self.nvtx):
+            self.actions.copy_(a.to(torch.int32), non_blocking=True)
+            _lib.check(self.lib.tc_step(_ptr(self.qubits), _ptr(self.syn), _ptr(self.actions), _ptr(self.reward),
+                                        _ptr(self.terminal), _ptr(self.status), self.d, self.n, _stream(self.device)),
+                       "tc_step")
+            self.steps += 1
         return self.reward, self.terminal
 
     def ground_state(self):
@@ -204,10 +237,12 @@ class ToricEngine:
         if self.out is None:
             self.ensure_capacity(self.worst_case_capacity())
         self.overflow.zero_()
-        _lib.check(self.lib.tc_perspectives_as(_ptr(syn), _ptr(self.out), OUT_DTYPES[self.out_dtype], _ptr(self.pos),
-                                               _ptr(self.counts), _ptr(self.offsets), _ptr(self.overflow), self.cap,
-                                               _ptr(self.workspace), self.workspace.numel(), self.d, n, _stream(self.device)),
-                   "tc_perspectives_as")
+        with _Range("toric/perspectives", self.nvtx):
+            _lib.check(self.lib.tc_perspectives_as(_ptr(syn), _ptr(self.out), OUT_DTYPES[self.out_dtype],
+                                                   _ptr(self.pos), _ptr(self.counts), _ptr(self.offsets),
+                                                   _ptr(self.overflow), self.cap, _ptr(self.workspace),
+                                                   self.workspace.numel(), self.d, n, _stream(self.device)),
+                       "tc_perspectives_as")
 
     def perspectives_count(self, syn=None, n=None):
         """Count + scan only (tc_persp_count): fills counts and offsets[n] = total, writes no perspectives."""
@@ -216,8 +251,12 @@ class ToricEngine:
         _lib.check(self.lib.tc_persp_count(_ptr(syn), _ptr(self.counts), _ptr(self.offsets), _ptr(self.workspace),
                                            self.workspace.numel(), self.d, n, _stream(self.device)), "tc_persp_count")
 
-    def actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
-                   freeze_done=False, actions_buffer=None, results=None, between=None):
+    def actor_step(self, *args, **kwargs):
+        with _Range("toric/actor_step", self.nvtx):
+            return self._actor_step(*args, **kwargs)
+
+    def _actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
+                    freeze_done=False, actions_buffer=None, results=None, between=None):
         """One fused actor iteration (asynchronous).  actions=None draws them on device; passing
         self.actions itself (e.g. filled by select_action) skips the copy; actions_buffer (device int32
         (n,4), 16-byte aligned) is read in place instead of self.actions.  freeze_done leaves envs whose
@@ -323,6 +362,39 @@ class ToricEngine:
             self.perspectives(syn=getattr(self, "_last_syn", None), n=n)
             total = self.total_perspectives(n)
         return self.out[:total], self.pos[:total], self.counts[:n], self.offsets[:n + 1]
+
+    # -- checkpoint / resume ---------------------------------------------------------------------
+    def state_dict(self):
+        """Everything a bit-exact resume needs (SURVEY.md section 5 "Checkpoint / resume"): the packed planes, the
+        per-env episode / step clocks, flags, thresholds and counters (cloned, on the device) plus the scalar
+        configuration.  The sampler is counter-based -- Philox keyed by (seed, global env id, episode, step) -- so there
+        is no generator state beyond `episode` and `steps`.  The perspective buffer is not part of the state: it is a
+        function of `syn` (perspectives() regenerates it)."""
+        sd = {name: getattr(self, name).clone() for name in self._STATE_TENSORS}
+        if self.prev_syn is not None:
+            sd["prev_syn"] = self.prev_syn.clone()
+        sd["meta"] = {"d": self.d, "n": self.n, "seed": self.seed, "env_base": self.env_base,
+                      "max_steps": self.max_steps, "out_dtype": str(self.out_dtype).replace("torch.", ""),
+                      "abi_version": _lib.ABI_VERSION}
+        return sd
+
+    def load_state_dict(self, sd):
+        """Restore a state_dict() into this engine (same d and n; seed / env_base / max_steps are taken from the
+        checkpoint so that the resumed trajectory is the saved one)."""
+        meta = sd["meta"]
+        if int(meta["d"]) != self.d or int(meta["n"]) != self.n:
+            raise ValueError("checkpoint is for d=%s n=%s, engine is d=%d n=%d" % (meta["d"], meta["n"], self.d, self.n))
+        if int(meta.get("abi_version", _lib.ABI_VERSION)) != _lib.ABI_VERSION:
+            raise ValueError("checkpoint was written under sampler / ABI version %s, this build is %d: the draw "
+                             "numbering differs, a resumed run would not continue the saved trajectory"
+                             % (meta.get("abi_version"), _lib.ABI_VERSION))
+        self.seed, self.env_base, self.max_steps = int(meta["seed"]), int(meta["env_base"]), int(meta["max_steps"])
+        for name in self._STATE_TENSORS:
+            getattr(self, name).copy_(sd[name])
+        if "prev_syn" in sd:
+            if self.prev_syn is None:
+                self.prev_syn = torch.zeros_like(self.syn)
+            self.prev_syn.copy_(sd["prev_syn"])
 
     def read_counters(self):
         c = self.counters.cpu().numpy()
