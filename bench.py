@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--dump-launches", action="store_true",
                     help="add the sum P and algorithmic bytes of every timed writer launch to the roofline object "
                          "(to match an ncu capture of one launch of the same command, scripts/gpu_traffic.sh)")
+    ap.add_argument("--single-pass", type=int, default=-1, choices=(-1, 0, 1),
+                    help="1: the one-kernel step (TC_ACTOR_SINGLE_PASS), 0: the three-kernel step, -1: the engine's default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -266,8 +268,10 @@ def run_b200(a):
 
     out_dtype = getattr(torch, a.out_dtype)
     esz = torch.empty((), dtype=out_dtype).element_size()
+    ekw = {} if a.single_pass < 0 else {"single_pass": bool(a.single_pass)}
     eng = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p,
-                          out_dtype=out_dtype)                                              # envs shard by rank
+                          out_dtype=out_dtype, **ekw)                                       # envs shard by rank
+    one_kernel = eng.single_pass and out_dtype is torch.float32 and d <= pkg.engine.SINGLE_PASS_MAX_D
     eng.ensure_capacity(eng.worst_case_capacity())
     max_steps = eng.max_steps
     prepare(a, eng)                             # reset, staggered episode clocks, untimed burn-in
@@ -287,10 +291,10 @@ def run_b200(a):
     # `a.sample_every`-th step is issued as its two halves with CUDA events around the writer launch, which
     # gives the dominant kernel's duration inside the timed region without putting two event records (and a
     # break of the programmatic dependent launch chain) into every step.
-    sampled = [k for k in range(a.steps) if k % a.sample_every == 0]
+    sampled = [] if one_kernel else [k for k in range(a.steps) if k % a.sample_every == 0]
     evb = {k: torch.cuda.Event(enable_timing=True) for k in sampled}
     evc = {k: torch.cuda.Event(enable_timing=True) for k in sampled}
-    totals = torch.zeros(len(sampled), dtype=torch.int64, device=dev)      # sum P of the sampled launches
+    totals = torch.zeros(max(len(sampled), 1), dtype=torch.int64, device=dev)      # sum P of the sampled launches
     barrier()
     with ClockSampler(local) as clk:
         ev0.record()
@@ -306,8 +310,12 @@ def run_b200(a):
         ev1.record()
         barrier()
     ms = ev0.elapsed_time(ev1)
-    write_ms = sum(evb[k].elapsed_time(evc[k]) for k in sampled) / len(sampled)
-    sampled_sum_p = float(totals.sum().item()) / len(sampled)
+    if one_kernel:          # the step IS the kernel: its launches run back to back, so step time = kernel time
+        write_ms = ms / a.steps
+        sampled_sum_p = float(eng.counters[5].item()) / a.steps
+    else:
+        write_ms = sum(evb[k].elapsed_time(evc[k]) for k in sampled) / len(sampled)
+        sampled_sum_p = float(totals.sum().item()) / len(sampled)
     per_launch_sum_p = [int(x) for x in totals.tolist()] if a.dump_launches else None
     ctr = eng.counters.clone()
     assert int(eng.overflow.item()) == 0
@@ -323,15 +331,17 @@ def run_b200(a):
     p_bar = sum_p_local / float(n * a.steps)
 
     peak, peak_src = load_peaks()
-    wbytes = write_kernel_bytes(d, n, sampled_sum_p, esz)      # the launches that were timed
+    wbytes = (b_alg(d, n, sampled_sum_p, esz) if one_kernel else
+              write_kernel_bytes(d, n, sampled_sum_p, esz))    # the launches that were timed
     achieved = wbytes / (write_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "persp_write_kernel<%d,%s>" % (d, a.out_dtype), "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": ("fused_step_kernel<%d,%s>" if one_kernel else "persp_write_kernel<%d,%s>")
+                % (d, a.out_dtype), "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                 # the kernel is a write-only stream and `peak` is a COPY (read+write) figure, so frac can exceed 1;
                 # write_peak is the write-only ceiling measured live (torch fill_ = a memset kernel, best of 5)
                 "write_peak": write_peak, "frac_of_write_peak": achieved / write_peak if write_peak else None,
                 "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
-                "kernel_launches_timed": len(sampled),
+                "kernel_launches_timed": a.steps if one_kernel else len(sampled),
                 "step_achieved": b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9}
     if per_launch_sum_p is not None:
         roofline["timed_launch_steps"] = sampled
@@ -358,7 +368,8 @@ def run_b200(a):
         torch.cuda.empty_cache()
 
         def make_engine():
-            e = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p, out_dtype=out_dtype)
+            e = pkg.ToricEngine(d, n, device=dev, seed=a.seed, env_base=rank * n, p_error=a.p, out_dtype=out_dtype,
+                                **ekw)
             e.ensure_capacity(e.worst_case_capacity())
             return e
         recorded = record_device_policy(a, make_engine, max(3, a.warmup) + a.steps)
@@ -388,7 +399,8 @@ def run_b200(a):
                            "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_open_loop": e2e_open,
                 "e2e_u8_full": e2e_u8,
-                "gpu_launches": 3 * a.steps,
+                "gpu_launches": (1 if one_kernel else 3) * a.steps,
+                "step_form": "single-pass (1 kernel)" if one_kernel else "three kernels (step+count, scan, writer)",
                 "clocks": clk.summary(), "nonce": _nonce(),
                 "counters": {k: c[k] for k in ("episodes", "solved", "ground_kept", "timeouts", "perspectives")}}
         print(json.dumps(line), flush=True)

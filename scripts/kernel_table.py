@@ -49,6 +49,8 @@ def main():
         n = a.scale * ((1 << 20) if d <= 9 else ((1 << 18) if d <= 16 else (1 << 16)))
         eng = pkg.ToricEngine(d, n, seed=0, p_error=0.1)
         eng.reset()
+        eng_lo = pkg.ToricEngine(d, n, seed=1, p_error=0.0005)
+        eng_mid = pkg.ToricEngine(d, n, seed=1, p_error=0.005)
         acts = torch.stack([torch.randint(0, 2, (n,)), torch.randint(0, d, (n,)), torch.randint(0, d, (n,)),
                             torch.randint(1, 4, (n,))], 1).to(torch.int32).cuda()
         eng.actions.copy_(acts)
@@ -62,6 +64,9 @@ def main():
                                                      pkg.engine._stream()), 2 * 6 * d * W + 16 + 5),
             ("tc_ground_state (K5)", lambda: eng.ground_state(), 4 * d * W + 1),
             ("tc_reset p=0.1 (K1)", lambda: eng.reset(), 6 * d * W + 4 + 8 + 1),
+            ("tc_reset p=0.005 (K1)", lambda: eng_mid.reset(), 6 * d * W + 4 + 8 + 1),
+            ("tc_reset p=0.0005 (K1)", lambda: eng_lo.reset(), 6 * d * W + 4 + 8 + 1),
+            ("tc_reset fixed weight 3 (K1)", lambda: eng_lo.reset(mode=1, n_fixed=3), 6 * d * W + 4 + 8 + 1),
             ("tc_persp_count + scan", lambda: eng.perspectives_count(), 2 * d * W + 4 + 4),
             ("tc_unpack_state", lambda: eng.get_state(), 2 * d * W + 2 * d * d),
             ("tc_pack_state", lambda: eng.set_state(u8), 2 * d * W + 2 * d * d),
