@@ -78,8 +78,15 @@ struct PerspCfg {
   static constexpr int kDD = D * D;
   static constexpr int kFields = (31 + D - 1) / D + 1;          // row fields overlapping one word
   static constexpr int kPlanesPerWord = 1 + (31 + D * D - 1) / (D * D);
-  static constexpr int kTabBytes = kPlane ? 4 * D * D * 8 : 4 * 2 * D * (int)sizeof(TabT);
-  static constexpr int kPosBytes = ((kPMax + 2) * 2 + 15) & ~15;
+  // Small lattices: an env's whole output is less than two 4 KB tiles (d=3: ~0.9 KB, d=4: ~3 KB, d=5: ~8 KB), so one
+  // warp per env spends its time on per-env setup and on expanding mostly empty tiles.  persp_write_group_kernel
+  // gives a warp kGroup CONSECUTIVE envs instead: their outputs are adjacent in memory, so they are written as ONE bit
+  // stream (one head / tail, full tiles in between) from kGroup plane tables.
+  static constexpr int kGroup = D == 3 ? 16 : (D == 4 ? 8 : (D == 5 ? 4 : 1));
+  static constexpr int kLanesPerEnv = D <= 4 ? 4 : 8;                       // load phase: lane = slot * kLanesPerEnv + row
+  static constexpr int kLoadRounds = kGroup * kLanesPerEnv > 32 ? kGroup * kLanesPerEnv / 32 : 1;
+  static constexpr int kTabBytes = kPlane ? kGroup * 4 * D * D * 8 : 4 * 2 * D * (int)sizeof(TabT);
+  static constexpr int kPosBytes = ((kGroup * kPMax + 2) * 2 + 15) & ~15;
   static constexpr int kAuxBytes = kPlane ? 4 * 16 * 4 : 0;      // plane path: the 4 x d base rows, doubled
   static constexpr int kCandBytes = kPlane ? ((2 * D * D * 8 + 127) & ~127) : 0;   // per-CTA candidate table
   // per-warp shared memory: [stage tiles][tab / planes][pos list][aux]
@@ -180,37 +187,27 @@ __device__ __forceinline__ void build_cand_table(unsigned char* smem, int nthrea
   }
 }
 
-// One env (or one slice of its tiles) by one warp: position list, base tables, bit stream -> staging tiles -> TMA
-// bulk stores.  v / pl: the env's syndrome rows (lane r holds row r), m0 / m1 its selection masks, P > 0 its
-// perspective count, off its first perspective's index in `out`.  pos_w: where positions go (nullptr for slices
-// other than 0).  `ring` counts the staging tiles this warp has pushed so far (keeps rotating across envs).
+// Position list of one env (reference order: matrix 0 row-major, then matrix 1 row-major), appended to the warp's
+// list at index kbase0; returns the list length afterwards.  slot: which plane table of the warp the env uses (plane
+// path with several envs per warp; 0 otherwise).  pos32 (nullable): the global (m,i,j,0) array, off: index of the
+// warp's FIRST perspective in it.
 template <int D, typename OutT>
-__device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t v, uint32_t pl, uint32_t m0,
-                                          uint32_t m1, int P, int64_t off, int slice, int split, uint32_t& ring,
-                                          OutT* __restrict__ out, uint8_t* __restrict__ pos_w, uint32_t one16) {
+__device__ __forceinline__ int env_positions(const WriterCtx<D, OutT>& cx, uint32_t m0, uint32_t m1, int kbase0,
+                                             int slot, uint32_t* __restrict__ pos32, int64_t off) {
   using Cfg = PerspCfg<D>;
-  using OC = OutCfg<OutT>;
-  constexpr int kE = OC::kE;
-  constexpr int kWordsPerLane = OC::kWordsPerLane;
-  constexpr int kTileElems = OC::kTileElems;
-  using TabT = typename Cfg::TabT;
   constexpr int G = D / 2;                       // grid_shift (src/Actor_mp.py:59)
   constexpr int DD = D * D;
   constexpr uint32_t kFull = 0xffffffffu;
-  constexpr uint32_t kRowMask = D >= 32 ? 0xffffffffu : ((1u << (D & 31)) - 1u);
   const int lane = cx.lane;
-  OutT* const stage = cx.stage;
-  unsigned char* const tab_raw = cx.tab_raw;
   uint16_t* const sp = cx.sp;
-  unsigned char* const aux = cx.aux;
   const uint2* const cand = cx.cand;
-  uint32_t* pos32 = reinterpret_cast<uint32_t*>(pos_w);
-
+  uint8_t* const pos_w = reinterpret_cast<uint8_t*>(pos32);
+  int kend;
   // ---- position list (reference order: matrix 0 row-major, then matrix 1 row-major) ----
   // One candidate qubit per lane and round; selected candidates are compacted in order with a ballot.
   // sp[k]: plane path = index of the c=0 rolled plane of perspective k; row path = m | r0<<1 | r1<<6.
   {
-    int kbase = 0;
+    int kbase = kbase0;
 #pragma unroll 1
     for (int q0 = 0; q0 < 2 * DD; q0 += 32) {
       const int q = q0 + lane;
@@ -222,7 +219,7 @@ __device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t
         const uint32_t bal = __ballot_sync(kFull, sel);
         if (sel) {
           const int k = kbase + __popc(bal & ((1u << lane) - 1u));
-          sp[k] = (uint16_t)cd.x;
+          sp[k] = (uint16_t)(cd.x + (uint32_t)(slot * 4 * DD));
           if (pos_w) pos32[off + k] = cd.y;
         }
         kbase += __popc(bal);
@@ -244,8 +241,23 @@ __device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t
         kbase += __popc(bal);
       }
     }
+    kend = kbase;
   }
+  return kend;
+}
 
+// Base tables of one env: t = 2m + c; row a of table t (see header).  Plane path: the 4*d*d rolled planes of the env
+// go to plane table `slot` of the warp.
+template <int D, typename OutT>
+__device__ __forceinline__ void env_tables(const WriterCtx<D, OutT>& cx, uint32_t v, uint32_t pl, int slot) {
+  using Cfg = PerspCfg<D>;
+  using TabT = typename Cfg::TabT;
+  constexpr int DD = D * D;
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr uint32_t kRowMask = D >= 32 ? 0xffffffffu : ((1u << (D & 31)) - 1u);
+  const int lane = cx.lane;
+  unsigned char* const tab_raw = cx.tab_raw;
+  unsigned char* const aux = cx.aux;
   // ---- base tables: t = 2m + c; row a of table t (see header) ----
   uint32_t tv = 0, tp = 0;
 #pragma unroll
@@ -255,7 +267,7 @@ __device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t
     if (lane == b) { tv = bv; tp = bp; }
   }
   if constexpr (Cfg::kPlane) {
-    unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw);
+    unsigned long long* planes = reinterpret_cast<unsigned long long*>(tab_raw) + slot * 4 * DD;
     uint32_t* rows = reinterpret_cast<uint32_t*>(aux);                         // [4][16]: rows doubled
     if (lane < D) {
       const int kv = (D - lane) % D, kp = D - 1 - lane;
@@ -302,7 +314,26 @@ __device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t
     }
   }
   __syncwarp();
+}
 
+// The warp's perspective list (P entries, positions and tables set up) as one bit stream -> staging tiles -> TMA bulk
+// stores, starting at perspective index `off` of `out`; (slice, split): this warp's share of the tiles.
+template <int D, typename OutT>
+__device__ __forceinline__ void stream_tiles(const WriterCtx<D, OutT>& cx, int P, int64_t off, int slice, int split,
+                                             uint32_t& ring, OutT* __restrict__ out, uint32_t one16) {
+  using Cfg = PerspCfg<D>;
+  using OC = OutCfg<OutT>;
+  constexpr int kE = OC::kE;
+  constexpr int kWordsPerLane = OC::kWordsPerLane;
+  constexpr int kTileElems = OC::kTileElems;
+  using TabT = typename Cfg::TabT;
+  constexpr int DD = D * D;
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr uint32_t kRowMask = D >= 32 ? 0xffffffffu : ((1u << (D & 31)) - 1u);
+  const int lane = cx.lane;
+  OutT* const stage = cx.stage;
+  unsigned char* const tab_raw = cx.tab_raw;
+  uint16_t* const sp = cx.sp;
   // ---- bit stream -> output tiles -> TMA bulk stores ----
   const int64_t f_start = off * (int64_t)(2 * DD);
   // phantom elements in front (owned by the previous env; even): the stream starts at the kAlignBytes boundary
@@ -420,6 +451,19 @@ __device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t
   __syncwarp();
 }
 
+// One env (or one slice of its tiles) by one warp: position list, base tables, stream.  v / pl: the env's syndrome rows
+// (lane r holds row r), m0 / m1 its selection masks, P > 0 its perspective count, off its first perspective's index in
+// `out`.  pos_w: where positions go (nullptr for slices other than 0).  `ring` counts the staging tiles this warp has
+// pushed so far (keeps rotating across envs).
+template <int D, typename OutT>
+__device__ __forceinline__ void write_env(const WriterCtx<D, OutT>& cx, uint32_t v, uint32_t pl, uint32_t m0,
+                                          uint32_t m1, int P, int64_t off, int slice, int split, uint32_t& ring,
+                                          OutT* __restrict__ out, uint8_t* __restrict__ pos_w, uint32_t one16) {
+  env_positions<D, OutT>(cx, m0, m1, 0, 0, reinterpret_cast<uint32_t*>(pos_w), off);
+  env_tables<D, OutT>(cx, v, pl, 0);
+  stream_tiles<D, OutT>(cx, P, off, slice, split, ring, out, one16);
+}
+
 template <int D, typename OutT>
 __global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
 persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
@@ -468,6 +512,74 @@ persp_write_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__
   __syncwarp();
   // the staging tiles must stay valid until the TMA engine has READ them; the global writes themselves complete
   // by grid end like any other store (same as a CUTLASS TMA-store epilogue's tma_store_wait<0>)
+  if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// Small lattices (PerspCfg<D>::kGroup > 1): one warp writes kGroup consecutive envs as one stream (see PerspCfg).
+template <int D, typename OutT>
+__global__ void __launch_bounds__(PerspCfg<D>::kWarps * 32)
+persp_write_group_kernel(const uint32_t* __restrict__ syn, const int32_t* __restrict__ local_off,
+                         const int64_t* __restrict__ block_off, OutT* __restrict__ out, uint8_t* __restrict__ pos,
+                         int64_t* __restrict__ offsets, int32_t* __restrict__ overflow, int64_t cap, int64_t n,
+                         uint32_t one16) {
+  using Cfg = PerspCfg<D>;
+  constexpr uint32_t kFull = 0xffffffffu;
+  constexpr int K = Cfg::kGroup, LPE = Cfg::kLanesPerEnv, R = Cfg::kLoadRounds, SPR = 32 / LPE;   // slots per round
+  static_assert(K == R * SPR, "group does not tile the load rounds");
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const WriterCtx<D, OutT> cx(smem, warp, lane);
+  build_cand_table<D>(smem, Cfg::kWarps * 32);
+  pdl_wait();
+  pdl_launch_dependents();
+  uint32_t ring = 0;
+  const int64_t n_items = (n + K - 1) / K;
+  const int64_t stride = (int64_t)gridDim.x * Cfg::kWarps;
+  for (int64_t item = (int64_t)blockIdx.x * Cfg::kWarps + warp; item < n_items; item += stride) {
+    const int64_t e0 = item * K;
+    // all loads first: lane = slot * LPE + row holds rows of env e0 + round * SPR + slot
+    uint32_t v_all[R], pl_all[R];
+#pragma unroll
+    for (int rd = 0; rd < R; ++rd) {
+      const int64_t e = e0 + rd * SPR + lane / LPE;
+      const int row = lane % LPE;
+      v_all[rd] = pl_all[rd] = 0;
+      if (e < n && row < D) {
+        v_all[rd] = __ldg(syn + e * 2 * D + row);
+        pl_all[rd] = __ldg(syn + e * 2 * D + D + row);
+      }
+    }
+    int64_t off = 0;
+    if (lane == 0) off = __ldg(block_off + e0 / Cfg::kEpb) + (int64_t)__ldg(local_off + e0);
+    off = __shfl_sync(kFull, off, 0);
+    int kbase = 0, ktrue = 0;                    // perspectives written / counted so far in this group
+    bool full = false;                           // capacity reached: this env and the ones behind it are skipped
+#pragma unroll
+    for (int s = 0; s < K; ++s) {
+      const int src = (s % SPR) * LPE + (lane < LPE ? lane : 0);
+      uint32_t v = __shfl_sync(kFull, v_all[s / SPR], src);
+      uint32_t pl = __shfl_sync(kFull, pl_all[s / SPR], src);
+      if (lane >= D) v = pl = 0;
+      if (e0 + s >= n) break;                    // warp-uniform
+      uint32_t m0, m1;
+      persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
+      const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
+      if (lane == 0) offsets[e0 + s] = off + ktrue;
+      ktrue += P;
+      if (P == 0) continue;
+      if (full || off + ktrue > cap) {           // offsets grow with the env index: once full, always full
+        if (lane == 0 && overflow) *overflow = 1;
+        full = true;
+        continue;
+      }
+      env_positions<D, OutT>(cx, m0, m1, kbase, s, reinterpret_cast<uint32_t*>(pos), off);
+      env_tables<D, OutT>(cx, v, pl, s);
+      kbase += P;
+    }
+    if (kbase > 0) stream_tiles<D, OutT>(cx, kbase, off, 0, 1, ring, out, one16);
+  }
+  __syncwarp();
   if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 

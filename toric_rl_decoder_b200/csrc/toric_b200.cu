@@ -534,6 +534,19 @@ int launch_write(const uint32_t* syn, const Workspace& w, OutT* out, uint8_t* po
 #define TC_WRITE_SPLIT 0          /* 0 = automatic */
 #endif
   if (w.epb != Cfg::kEpb) return -1;          // the count kernels' CTA shape is baked into the writer
+#ifndef TC_NO_GROUP_WRITER
+  if constexpr (Cfg::kGroup > 1) {            // small lattices: kGroup consecutive envs per warp, one stream
+    static std::once_flag once_g[64];
+    std::call_once(once_g[dev], [] {
+      cudaFuncSetAttribute(persp_write_group_kernel<D, OutT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           Cfg::kSmemBytes);
+    });
+    const int64_t items = (n + Cfg::kGroup - 1) / Cfg::kGroup;
+    launch_pdl(persp_write_group_kernel<D, OutT>, grid_for(items, WPB), WPB * 32, Cfg::kSmemBytes, st, syn,
+               (const int32_t*)w.local_off, (const int64_t*)w.block_off, out, pos, offsets, overflow, cap, n, one16);
+    return 0;
+  }
+#endif
   int split = 1;
   if (!Cfg::kPlane) {
     if (TC_WRITE_SPLIT > 0) {
