@@ -160,6 +160,34 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
                  uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
                  size_t workspace_bytes, int d, int64_t n, void* stream);
 
+/* Host-buffer form of one actor iteration: what the reference's actor does around EnvSet.step with HOST arrays
+ * (src/Actor_mp.py:116-125, src/EnvSet.py:38-47) -- actions come from pinned host memory, rewards / terminals /
+ * perspective counts / new states go back to pinned host memory, the perspective tensor stays on the device
+ * (`.to(device)`, src/numba/util_actor.py:39).  ONE call enqueues, without ever blocking the host,
+ *   h2d stream:      actions -> d_actions;                                  record ev_actions
+ *   compute stream:  wait ev_actions [, ev_unpacked_prev]; tc_actor_pre (results written straight into d_stage);
+ *                    record ev_compute; tc_persp_write_as
+ *   d2h stream:      wait ev_compute; new states -> d_stage + o_state (state_mode 1: tc_unpack_state, 2:
+ *                    tc_state_rows, 0: none); record ev_unpacked; d_stage -> h_stage; record ev_result
+ * so the step's results, final before the perspective writer runs, cross PCIe underneath the writer.  The caller
+ * waits on ev_result (cudaEventSynchronize) before it reads h_stage.  Streams and events are the caller's
+ * (cudaStream_t / cudaEvent_t as void*); the library creates nothing.  d_stage / h_stage layout: float32 reward [n]
+ * at o_reward, int32 counts [n] at o_counts, uint8 terminal [n] at o_term, states at o_state (16-byte aligned).
+ * ev_unpacked_prev (nullable): the ev_unpacked of the previous call -- this step's kernels rewrite the syndromes
+ * that call's state kernel reads. */
+typedef struct tc_host_step {
+  uint32_t* qubits; uint32_t* syn; uint32_t* prev_syn; uint8_t* gs; uint8_t* status; int32_t* steps;
+  uint32_t* episode; const uint32_t* p_thresh; int64_t* counters; int64_t* offsets; int32_t* overflow;
+  void* out; uint8_t* pos; int64_t cap; int out_dtype;
+  void* workspace; size_t workspace_bytes;
+  int flags, max_steps, mode, n_fixed; uint64_t seed; int64_t env_base; int d; int64_t n;
+  const int32_t* h_actions; int32_t* d_actions; uint8_t* d_stage; uint8_t* h_stage; size_t stage_bytes;
+  size_t o_reward, o_counts, o_term, o_state; int state_mode;
+  void* h2d_stream; void* compute_stream; void* d2h_stream;
+  void* ev_actions; void* ev_compute; void* ev_unpacked_prev; void* ev_unpacked; void* ev_result;
+} tc_host_step;
+int tc_host_actor_step(const tc_host_step* s);
+
 /* ---- policy-side entry points (the callers either side of the env path) ---- */
 
 /* _selectActionBatch_prime + the epsilon-greedy draw of selectActionBatch (src/numba/util_actor.py:41-107;

@@ -35,6 +35,24 @@ def test_binding_covers_header(lib_path):
     _lib.load()
 
 
+def test_host_step_struct_layout_matches_header(tmp_path):
+    """_lib.HostStep (ctypes) against struct tc_host_step as the C compiler lays it out: size and every field offset."""
+    import subprocess
+    from toric_rl_decoder_b200 import _lib
+    names = [f[0] for f in _lib.HostStep._fields_]
+    src = ['#include <stdio.h>', '#include <stddef.h>', '#include "toric_b200.h"', 'int main(void) {',
+           '  printf("%zu\\n", sizeof(tc_host_step));']
+    src += ['  printf("%%zu\\n", offsetof(tc_host_step, %s));' % n for n in names]
+    src += ['  return 0;', '}']
+    c = tmp_path / "layout.c"
+    c.write_text("\n".join(src))
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(c)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    assert got[0] == ctypes.sizeof(_lib.HostStep)
+    assert got[1:] == [getattr(_lib.HostStep, n).offset for n in names]
+
+
 def test_argument_validation_without_gpu(lib_path):
     from toric_rl_decoder_b200 import _lib
     lib = _lib.load()
@@ -45,6 +63,10 @@ def test_argument_validation_without_gpu(lib_path):
     assert lib.tc_syndrome(None, None, 7, 10, None) == -1
     assert lib.tc_step(None, None, None, None, None, None, 7, 10, None) == -1
     assert lib.tc_persp_write_as(None, None, 0, None, None, None, 0, None, 0, 7, 10, None) == -1
+    assert lib.tc_host_actor_step(None) == -1
+    hs = _lib.HostStep()
+    hs.d, hs.n = 7, 16
+    assert lib.tc_host_actor_step(ctypes.byref(hs)) == -1          # no streams / events / buffers
 
 
 def test_no_cpu_fallback():

@@ -11,6 +11,20 @@ from .buildlib import LIB_PATH
 _c = ctypes
 _vp, _i, _i64, _u64, _sz = _c.c_void_p, _c.c_int, _c.c_int64, _c.c_uint64, _c.c_size_t
 
+class HostStep(_c.Structure):
+    """struct tc_host_step of include/toric_b200.h (argument block of tc_host_actor_step), field for field."""
+    _fields_ = [(n, _vp) for n in ("qubits", "syn", "prev_syn", "gs", "status", "steps", "episode", "p_thresh",
+                                   "counters", "offsets", "overflow", "out", "pos")] + \
+               [("cap", _i64), ("out_dtype", _i), ("workspace", _vp), ("workspace_bytes", _sz),
+                ("flags", _i), ("max_steps", _i), ("mode", _i), ("n_fixed", _i), ("seed", _u64), ("env_base", _i64),
+                ("d", _i), ("n", _i64)] + \
+               [(n, _vp) for n in ("h_actions", "d_actions", "d_stage", "h_stage")] + \
+               [("stage_bytes", _sz), ("o_reward", _sz), ("o_counts", _sz), ("o_term", _sz), ("o_state", _sz),
+                ("state_mode", _i)] + \
+               [(n, _vp) for n in ("h2d_stream", "compute_stream", "d2h_stream", "ev_actions", "ev_compute",
+                                   "ev_unpacked_prev", "ev_unpacked", "ev_result")]
+
+
 # name -> argtypes, exactly the prototypes of include/toric_b200.h
 SIGNATURES = {
     "tc_abi_version": [],
@@ -33,6 +47,7 @@ SIGNATURES = {
                      _vp, _vp, _vp, _sz, _i, _i64, _vp],
     "tc_actor_step": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _u64, _i64,
                       _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_host_actor_step": [_c.POINTER(HostStep)],
     "tc_select_action": [_vp, _vp, _vp, _vp, _vp, _vp, _c.c_uint32, _vp, _u64, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
     "tc_transitions": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i64, _vp],
     "tc_td_priorities": [_vp, _vp, _vp, _vp, _c.c_float, _vp, _i64, _vp],

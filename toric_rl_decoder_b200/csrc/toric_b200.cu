@@ -845,6 +845,40 @@ int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* 
   return tc_persp_write(syn, out, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n, stream);
 }
 
+int tc_host_actor_step(const tc_host_step* s) {
+  if (!s || bad_d(s->d) || s->n < 0) return -1;
+  if (s->state_mode < 0 || s->state_mode > 2) return -1;
+  if (s->n == 0) return 0;
+  if (!s->h_actions || !s->d_actions || !s->d_stage || !s->h_stage || !s->h2d_stream || !s->compute_stream ||
+      !s->d2h_stream || !s->ev_actions || !s->ev_compute || !s->ev_result || (s->state_mode && !s->ev_unpacked))
+    return -1;
+  if ((s->o_reward & 3) || (s->o_counts & 3) || (s->o_state & 15)) return -1;
+  cudaStream_t h2d = (cudaStream_t)s->h2d_stream, cs = (cudaStream_t)s->compute_stream, d2h = (cudaStream_t)s->d2h_stream;
+  cudaMemcpyAsync(s->d_actions, s->h_actions, (size_t)s->n * 16, cudaMemcpyHostToDevice, h2d);
+  cudaEventRecord((cudaEvent_t)s->ev_actions, h2d);
+  cudaStreamWaitEvent(cs, (cudaEvent_t)s->ev_actions, 0);
+  if (s->ev_unpacked_prev) cudaStreamWaitEvent(cs, (cudaEvent_t)s->ev_unpacked_prev, 0);
+  float* reward = reinterpret_cast<float*>(s->d_stage + s->o_reward);
+  int32_t* counts = reinterpret_cast<int32_t*>(s->d_stage + s->o_counts);
+  uint8_t* terminal = s->d_stage + s->o_term;
+  int rc = tc_actor_pre(s->qubits, s->syn, s->prev_syn, s->d_actions, reward, terminal, s->gs, s->status, s->steps,
+                        s->episode, s->p_thresh, s->counters, s->flags, s->max_steps, s->mode, s->n_fixed, s->seed,
+                        s->env_base, counts, s->offsets, s->workspace, s->workspace_bytes, s->d, s->n, cs);
+  if (rc != 0) return rc;
+  cudaEventRecord((cudaEvent_t)s->ev_compute, cs);
+  rc = tc_persp_write_as(s->syn, s->out, s->out_dtype, s->pos, s->offsets, s->overflow, s->cap, s->workspace,
+                         s->workspace_bytes, s->d, s->n, cs);
+  if (rc != 0) return rc;
+  cudaStreamWaitEvent(d2h, (cudaEvent_t)s->ev_compute, 0);
+  if (s->state_mode == 1) rc = tc_unpack_state(s->syn, s->d_stage + s->o_state, s->d, s->n, d2h);
+  else if (s->state_mode == 2) rc = tc_state_rows(s->syn, s->d_stage + s->o_state, s->d, s->n, d2h);
+  if (rc != 0) return rc;
+  if (s->state_mode) cudaEventRecord((cudaEvent_t)s->ev_unpacked, d2h);
+  cudaMemcpyAsync(s->h_stage, s->d_stage, s->stage_bytes, cudaMemcpyDeviceToHost, d2h);
+  cudaEventRecord((cudaEvent_t)s->ev_result, d2h);
+  return launch_status();
+}
+
 // ---- policy-side entry points ---------------------------------------------
 
 int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* offsets, const uint32_t* episode,

@@ -19,8 +19,10 @@ puts it (`.to(device)`, src/numba/util_actor.py:39).
 import numpy as np
 import torch
 
+import ctypes
+
 from . import _lib
-from .engine import _ptr
+from .engine import ACTOR_AUTO_RESET, _Range
 
 
 class LazyStates:
@@ -114,6 +116,8 @@ class HostActorPipeline:
                 "ev_unpacked": torch.cuda.Event(),
                 "busy": False,
             }
+            for name in ("ev_actions", "ev_compute", "ev_result", "ev_unpacked"):
+                slot[name].record(self.h2d_stream)        # torch creates the cudaEvent_t on first use
             hs = slot["h_stage"].numpy()
             slot["views"] = {
                 "reward": hs[self.o_reward:self.o_reward + 4 * n].view(np.float32),
@@ -137,42 +141,61 @@ class HostActorPipeline:
         self.collected = 0
         self._ev_unpacked = None
 
-    def submit(self, actions_host, auto_reset=True):
+    def _native_block(self, slot):
+        """The slot's tc_host_step argument block (include/toric_b200.h): everything that does not change from step to
+        step is filled once; submit() only updates the action pointer, the flags and the event of the previous step."""
+        from .engine import OUT_DTYPES
+        eng = self.eng
+        hs = _lib.HostStep()
+        for name in ("qubits", "syn", "status", "steps", "episode", "p_thresh", "counters", "offsets", "overflow",
+                     "out", "pos", "workspace"):
+            setattr(hs, name, getattr(eng, name).data_ptr())
+        hs.gs = eng.step_gs.data_ptr()
+        hs.prev_syn = None
+        hs.cap, hs.out_dtype = eng.cap, OUT_DTYPES[eng.out_dtype]
+        hs.workspace_bytes = eng.workspace.numel()
+        hs.max_steps, hs.mode, hs.n_fixed = eng.max_steps, 0, 0
+        hs.seed, hs.env_base, hs.d, hs.n = eng.seed, eng.env_base, eng.d, eng.n
+        hs.d_actions, hs.d_stage = slot["d_actions"].data_ptr(), slot["d_stage"].data_ptr()
+        hs.h_stage, hs.stage_bytes = slot["h_stage"].data_ptr(), self.nbytes
+        hs.o_reward, hs.o_counts, hs.o_term, hs.o_state = self.o_reward, self.o_counts, self.o_term, self.o_state
+        hs.state_mode = {"u8": 1, "rows": 2, "lazy": 2, None: 0}[self.states]
+        hs.h2d_stream, hs.d2h_stream = self.h2d_stream.cuda_stream, self.d2h_stream.cuda_stream
+        for name in ("ev_actions", "ev_compute", "ev_unpacked", "ev_result"):
+            setattr(hs, name, slot[name].cuda_event)
+        return hs
+
+    def submit(self, actions_host, auto_reset=True, mode=0, n_fixed=0):
         """Enqueue one step.  actions_host: pinned int32 tensor (n,4).  Never blocks the host unless the
         ring is full (then the oldest result must be collected first).
 
         The step's results (reward, terminal, counts, new states) are final once the step / count kernels have
-        run, i.e. BEFORE the perspective writer: an event is recorded there, and the state unpack kernel and the
-        download run on the d2h stream behind that event, overlapping the writer.  The next step's first kernel
-        waits for the unpack (it rewrites the syndromes the unpack reads)."""
+        run, i.e. BEFORE the perspective writer: an event is recorded there, and the state kernel and the download
+        run on the d2h stream behind that event, overlapping the writer.  The next step's first kernel waits for
+        the state kernel (it rewrites the syndromes that kernel reads).  The whole sequence -- upload, event edges,
+        three kernels, state kernel, download -- is enqueued by ONE native call (tc_host_actor_step): a closed-loop
+        caller's turn-around is then the PCIe round trip, not a few hundred microseconds of Python."""
         if self.submitted - self.collected >= self.depth:
             raise RuntimeError("pipeline full: collect() before submitting again")
         eng = self.eng
+        if actions_host.dtype != torch.int32 or tuple(actions_host.shape) != (eng.n, 4) or not actions_host.is_contiguous():
+            raise ValueError("actions_host must be a contiguous int32 tensor of shape (%d, 4)" % eng.n)
+        if eng.out is None:
+            eng.ensure_capacity(eng.worst_case_capacity())
         slot = self.slots[self.submitted % self.depth]
-        compute = torch.cuda.current_stream(eng.device)
-        with torch.cuda.stream(self.h2d_stream):
-            slot["d_actions"].copy_(actions_host, non_blocking=True)
-            slot["ev_actions"].record(self.h2d_stream)
-        compute.wait_event(slot["ev_actions"])
-        if self._ev_unpacked is not None:
-            compute.wait_event(self._ev_unpacked)         # the previous step's unpack has read eng.syn
-        # the step writes reward / terminal / counts straight into the slot's download block
-        eng.actor_step(auto_reset=auto_reset, actions_buffer=slot["d_actions"],
-                       results=(slot["d_reward"], slot["d_term"], slot["d_counts"]),
-                       between=lambda: slot["ev_compute"].record(compute))
-        with torch.cuda.stream(self.d2h_stream):
-            self.d2h_stream.wait_event(slot["ev_compute"])
-            if self.states == "u8":
-                _lib.check(eng.lib.tc_unpack_state(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
-                                                   self.d2h_stream.cuda_stream), "tc_unpack_state")
-            elif self.states in ("rows", "lazy"):
-                _lib.check(eng.lib.tc_state_rows(_ptr(eng.syn), _ptr(slot["d_state"]), eng.d, eng.n,
-                                                 self.d2h_stream.cuda_stream), "tc_state_rows")
-            if self.states is not None:
-                slot["ev_unpacked"].record(self.d2h_stream)
-                self._ev_unpacked = slot["ev_unpacked"]
-            slot["h_stage"].copy_(slot["d_stage"], non_blocking=True)
-            slot["ev_result"].record(self.d2h_stream)
+        hs = slot.get("native")
+        if hs is None or hs.cap != eng.cap or hs.out != eng.out.data_ptr():
+            hs = slot["native"] = self._native_block(slot)
+        hs.h_actions = actions_host.data_ptr()
+        hs.flags = ACTOR_AUTO_RESET if auto_reset else 0
+        hs.mode, hs.n_fixed = int(mode), int(n_fixed)
+        hs.compute_stream = torch.cuda.current_stream(eng.device).cuda_stream
+        hs.ev_unpacked_prev = self._ev_unpacked.cuda_event if self._ev_unpacked is not None else None
+        eng._last_syn = eng.syn
+        with _Range("toric/host_actor_step", eng.nvtx):
+            _lib.check(eng.lib.tc_host_actor_step(ctypes.byref(hs)), "tc_host_actor_step")
+        if self.states is not None:
+            self._ev_unpacked = slot["ev_unpacked"]
         self.submitted += 1
 
     def collect(self):
