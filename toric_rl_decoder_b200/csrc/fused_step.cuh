@@ -152,6 +152,10 @@ fused_step_kernel(const ActorArgs a, const ScanWs ws, OutT* __restrict__ out, ui
   const int64_t e = (int64_t)blockIdx.x * Cfg::kWarps + warp;
   uint32_t ring = 0;
   if (e < a.n) {                                  // warp-uniform
+#ifdef TC_FUSED_TIMING
+    unsigned long long t_start;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_start));
+#endif
     const uint32_t launch = *ws.header;
     const uint32_t epoch = launch % 0xfffffu + 1u;             // never 0: zero-filled descriptors are "not ready"
     const int r = lane;
@@ -224,7 +228,23 @@ fused_step_kernel(const ActorArgs a, const ScanWs ws, OutT* __restrict__ out, ui
       a.episode[e] = ep;
       a.counts[e] = P;
     }
+#ifdef TC_FUSED_TIMING   /* diagnostic build: per-env phase durations (ns >> 4, 16 bits each) into the unused local_off */
+    unsigned long long t_pub;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_pub));
+#endif
+#ifdef TC_FUSED_NO_LOOKBACK   /* diagnostic build: no scan at all, every env writes at its worst-case slot */
+    const long long off = (long long)e * (2 * D * D);
+#else
     const long long off = lookback_offset(ws, epoch, e, P, lane);
+#endif
+#ifdef TC_FUSED_TIMING
+    {
+      unsigned long long t_done;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_done));
+      const unsigned long long pre = (t_pub - t_start) >> 4, wait = (t_done - t_pub) >> 4;
+      if (lead) a.local_off[e] = (int)((pre > 0xffffull ? 0xffffull : pre) | ((wait > 0xffffull ? 0xffffull : wait) << 16));
+    }
+#endif
     if (lead) offsets[e] = off;
     if (e == a.n - 1 && lead) {                    // every other env has published (and read the launch counter)
       offsets[a.n] = off + P;
