@@ -8,7 +8,9 @@ Prints one JSON line per p with the failure counts next to both reference runs
 With --d 5 the same sweep on the second lattice size the reference published (results/evaluation_size_5.txt,
 network/converged/Size_5_NN_11_17_Mar_2020_22_33_59.pt, q = 3 forced errors).
 
-  python scripts/c4_big.py [--d 7|5] [--scale 1.0]
+  python scripts/c4_big.py [--d 7|5] [--scale 1.0] [--n 10000000]
+  torchrun --nproc-per-node 8 ... scripts/c4_big.py --n 10000000      # episodes sharded over the ranks by global index,
+                                                                      # sums all-reduced (evaluation._evaluate_one_p)
 """
 import argparse
 import json
@@ -21,7 +23,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from toric_rl_decoder_b200 import evaluation, networks  # noqa: E402
+from toric_rl_decoder_b200 import evaluation, networks, sharding  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
 # ground-state rate, P_l, mean steps: (data/evaluation_size_7_p_<p>.txt:2, results/evaluation_size_7.txt) -- 2e6 episodes each
@@ -39,7 +41,12 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--d", type=int, default=7, choices=(5, 7))
+    ap.add_argument("--n", type=int, default=0, help="syndromes per p (overrides the built-in sizes)")
+    ap.add_argument("--n-high-p", type=int, default=0, help="syndromes at p = 0.05 (default: --n)")
     a = ap.parse_args()
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    rank, world, local = sharding.init_from_env("nccl")
     d = a.d
     weights = {7: "Size_7_NN_11_random_state.pt", 5: "Size_5_NN_11_converged_state.pt"}[d]
     ref_table = REF if d == 7 else REF5
@@ -50,6 +57,8 @@ def main():
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
+    if a.n:
+        sizes = tuple((p, (a.n_high_p or a.n) if p >= 0.05 else a.n) for p, _ in sizes)
     for p, n in sizes:
         n = max(1024, int(n * a.scale))
         t0 = time.perf_counter()
@@ -57,7 +66,9 @@ def main():
             model, "toric-code-v0", cfg, d // 2, "cuda", [p], num_of_episodes=n, num_of_steps=75,
             nbr_of_qubit_errors=d // 2 + 1, seed=11, keep_failed=False)
         torch.cuda.synchronize()
-        wall = time.perf_counter() - t0
+        wall = sharding.max_over_ranks(time.perf_counter() - t0, torch.device("cuda", local))
+        if rank != 0:
+            continue
         (g_ref, pl_ref, st_ref), g_ref2 = ref_table[p]
         f = 1.0 - float(gs[0])
 
@@ -67,7 +78,7 @@ def main():
             return (f - fo) / math.sqrt(max(pooled * (1 - pooled), 1e-30) * (1.0 / n + 1.0 / N_REF))
         print(json.dumps({
             "config": "c4 d=%d importance-sampled sweep (NN_11 Size_%d converged weights, TF32 conv, padded channels)" % (d, d),
-            "p_error": p, "syndromes": n, "failures": int(round(f * n)), "failure_rate": f,
+            "p_error": p, "n_gpus": world, "syndromes": n, "failures": int(round(f * n)), "failure_rate": f,
             "failure_rate_reference_data": 1 - g_ref,
             "failure_rate_reference_results": (1 - g_ref2) if g_ref2 is not None else None,
             "z_vs_reference_data": z(g_ref), "z_vs_reference_results": z(g_ref2) if g_ref2 is not None else None,
@@ -77,6 +88,8 @@ def main():
             "mean_steps_reference": st_ref, "mean_q": float(mq[0]), "failures_by_initial_weight": {
                 str(int(k)): int(v) for k, v in zip(hist[0], hist[2]) if v > 0},
             "syndromes_per_s": n / wall, "seconds": wall}), flush=True)
+    if world > 1:
+        torch.distributed.destroy_process_group()
 
 
 if __name__ == "__main__":
