@@ -16,7 +16,7 @@ from toric_rl_decoder_b200 import sharding  # noqa: E402
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--global-envs", type=int, default=1 << 20)
-    ap.add_argument("--cases", default="15:0.05,15:0.2,25:0.05,25:0.2")
+    ap.add_argument("--cases", default="15:0.05,15:0.1,15:0.2,25:0.05,25:0.1,25:0.2")
     ap.add_argument("--steps", type=int, default=3)
     a = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
