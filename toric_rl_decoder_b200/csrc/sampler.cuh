@@ -31,6 +31,8 @@
 //    already occupied; code = 1 + mulhi(w1, 3).  Mode 2 then overlays the depolarizing field on the qubits
 //    that are still free (occupied qubits keep their slot and, if it says "error", their code chunks).
 #pragma once
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace tc {
@@ -46,16 +48,35 @@ __device__ __forceinline__ uint32_t word_of(const uint4& v, int k) {
   return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
 }
 
+// Index of the first error of a depolarizing field conditioned on holding at least one: truncated geometric law
+// P(K = k) = (1-p)^k p / (1 - (1-p)^nq), drawn by inversion from a 53-bit uniform (w0, w1 of the kDomFirst call).
+// Not inlined: the double-precision logarithms would otherwise cost the whole sampler ~25 registers of occupancy for a
+// path only low-p resets take.
+__device__ __noinline__ int first_error_index(uint32_t thresh, int nq, uint32_t w0, uint32_t w1) {
+  const double log_q = log1p(-(double)thresh * (1.0 / 4294967296.0));        // log(1 - p)
+  const double mass = -expm1((double)nq * log_q);                            // 1 - (1-p)^nq
+  const unsigned long long u53 = (((unsigned long long)w0 << 32) | (unsigned long long)w1) >> 11;
+  const double u = (double)u53 * (1.0 / 9007199254740992.0);
+  const double k = floor(log1p(-u * mass) / log_q);
+  return k >= (double)(nq - 1) ? nq - 1 : (k > 0.0 ? (int)k : 0);
+}
+
+__device__ __forceinline__ int first_set(uint32_t m) { return __ffs((int)m) - 1; }
+__device__ __forceinline__ int first_set(unsigned long long m) { return __ffsll((long long)m) - 1; }
+
 // Depolarizing field of one lattice row (both matrices).  first_q: linear index of the forced first error, or
-// -1 (unconditioned).  Returns the row's x / z planes of matrix 0 and 1.
+// -1 (unconditioned).  Returns the row's x / z planes of matrix 0 and 1.  M: the row's slot mask type -- uint32_t while
+// 2d <= 32 (group sizes 8 and 16), unsigned long long above (half the instructions of the 64-bit form where it fits).
+template <typename M>
 __device__ __forceinline__ void depolarize_row(int d, int row, uint32_t elo, uint32_t ehi, uint32_t episode,
                                                uint32_t attempt, uint32_t thresh, uint2 key, int first_q,
                                                uint32_t& x0, uint32_t& z0, uint32_t& x1, uint32_t& z1) {
+  constexpr int kBits = (int)sizeof(M) * 8;
   const uint32_t t_hi = thresh >> 16, t_lo = thresh & 0xffffu;
   const uint32_t base = (attempt << 10) | ((uint32_t)row << 5);
   const int nslots = 2 * d;
   const int ncalls = (nslots + 7) >> 3;
-  unsigned long long err = 0, bnd = 0;          // bit s = qubit s of the row
+  M err = 0, bnd = 0;                            // bit s = qubit s of the row
   uint4 rnd = make_uint4(0, 0, 0, 0);
 #pragma unroll 1
   for (int c = 0; c < ncalls; ++c) {
@@ -68,49 +89,57 @@ __device__ __forceinline__ void depolarize_row(int d, int row, uint32_t elo, uin
       lt |= (uint32_t)(u < t_hi) << h;
       eq |= (uint32_t)(u == t_hi) << h;
     }
-    err |= (unsigned long long)lt << (8 * c);
-    bnd |= (unsigned long long)eq << (8 * c);
+    err |= (M)lt << (8 * c);
+    bnd |= (M)eq << (8 * c);
   }
-  const unsigned long long live = nslots >= 64 ? ~0ull : ((1ull << nslots) - 1ull);
+  const M live = nslots >= kBits ? ~(M)0 : (((M)1 << nslots) - (M)1);
   err &= live;
   bnd &= live;
   while (bnd) {                                  // probability 2^-16 per qubit: draw the uniform's low half
-    const int s = __ffsll((long long)bnd) - 1;
+    const int s = first_set(bnd);
     bnd &= bnd - 1;
     const uint4 r = philox4x32_10(make_uint4(elo, ehi, episode, base | (uint32_t)(16 + (s >> 2))), key);
-    if ((word_of(r, s & 3) & 0xffffu) < t_lo) err |= 1ull << s;
+    if ((word_of(r, s & 3) & 0xffffu) < t_lo) err |= (M)1 << s;
   }
   if (first_q >= 0) {                            // qubits before the first error are clean, the first one errs
     const int dd = d * d;
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
       const int rel = first_q - (m * dd + row * d);        // column of the first error inside this row, if any
-      unsigned long long clean = rel <= 0 ? 0ull : (rel >= d ? ((1ull << d) - 1ull) : ((1ull << rel) - 1ull));
-      unsigned long long one = (rel >= 0 && rel < d) ? (1ull << rel) : 0ull;
+      const M clean = rel <= 0 ? (M)0 : (rel >= d ? (((M)1 << d) - (M)1) : (((M)1 << rel) - (M)1));
+      const M one = (rel >= 0 && rel < d) ? ((M)1 << rel) : (M)0;
       err = (err & ~(clean << (m * d))) | (one << (m * d));
     }
   }
-  // Pauli codes: 2-bit chunks behind the last slot, chunk 0 rejected
-  unsigned long long xs = 0, zs = 0;
+  // Pauli codes: 2-bit chunks from the words behind the last slot (2d is even, so the stream starts on a word
+  // boundary: word (2d % 8) / 2 of the last call, or the next call when that one is full), chunk 0 rejected
+  M xs = 0, zs = 0;
   int c = ncalls - 1;
-  int pos = 16 * (nslots & 7);
-  if (pos == 0) pos = 128;                       // the last call is full: the stream starts with the next call
-  unsigned long long todo = err;
+  int wi = (nslots & 7) ? ((nslots & 7) >> 1) : 4;   // next word of the current call (4 = exhausted)
+  uint32_t cur = 0;
+  int left = 0;                                  // chunks left in `cur`
+  M todo = err;
   while (todo) {
-    const int s = __ffsll((long long)todo) - 1;
+    const int s = first_set(todo);
     todo &= todo - 1;
     uint32_t v;
     do {
-      if (pos >= 128) {
-        ++c;
-        rnd = philox4x32_10(make_uint4(elo, ehi, episode, base | (uint32_t)(c & 15)), key);
-        pos = 0;
+      if (left == 0) {
+        if (wi == 4) {
+          ++c;
+          rnd = philox4x32_10(make_uint4(elo, ehi, episode, base | (uint32_t)(c & 15)), key);
+          wi = 0;
+        }
+        cur = word_of(rnd, wi);
+        ++wi;
+        left = 16;
       }
-      v = (word_of(rnd, pos >> 5) >> (pos & 31)) & 3u;
-      pos += 2;
+      v = cur & 3u;
+      cur >>= 2;
+      --left;
     } while (v == 0u);
-    if (v != 3u) xs |= 1ull << s;                // 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3}
-    if (v != 1u) zs |= 1ull << s;
+    if (v != 3u) xs |= (M)1 << s;                // 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3}
+    if (v != 1u) zs |= (M)1 << s;
   }
   const uint32_t rm = row_mask(d);
   x0 = (uint32_t)xs & rm;
@@ -128,9 +157,7 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
   mode &= 3;
   const int nq = 2 * d * d;
   const int nf = n_fixed < nq ? n_fixed : nq;
-  uint32_t pm = 1;
-  while ((int)pm < nq) pm <<= 1;
-  pm -= 1;
+  const uint32_t pm = 0xffffffffu >> __clz(nq - 1);      // smallest 2^k - 1 >= nq - 1 (nq >= 18)
   const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
   const uint32_t cap = (mode == 0) ? kMaxAttempts : kMaxFixedAttempts;
   const bool conditioned = mode == 0 && !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
@@ -142,11 +169,6 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
     st.attempts = 1;
     st.nx = st.ny = st.nz = 0;
     return;
-  }
-  double log_q = 0.0, mass = 0.0;                // log(1-p), 1 - (1-p)^nq
-  if (conditioned) {
-    log_q = log1p(-(double)thresh * (1.0 / 4294967296.0));
-    mass = -expm1((double)nq * log_q);
   }
   while (true) {
     s.x0 = s.x1 = s.z0 = s.z1 = 0;
@@ -179,15 +201,13 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
       int first_q = -1;
       if (conditioned) {
         const uint4 rf = philox4x32_10(make_uint4(elo, ehi, episode, kDomFirst | attempt), key);
-        const unsigned long long u53 = (((unsigned long long)rf.x << 32) | (unsigned long long)rf.y) >> 11;
-        const double u = (double)u53 * (1.0 / 9007199254740992.0);
-        const double k = floor(log1p(-u * mass) / log_q);
-        first_q = k >= (double)(nq - 1) ? nq - 1 : (k > 0.0 ? (int)k : 0);
+        first_q = first_error_index(thresh, nq, rf.x, rf.y);
       }
       if (r < d) {
         const uint32_t occ0 = s.x0 | s.z0, occ1 = s.x1 | s.z1;
         uint32_t x0, z0, x1, z1;
-        depolarize_row(d, r, elo, ehi, episode, attempt, thresh, key, first_q, x0, z0, x1, z1);
+        using Mask = typename std::conditional<(G <= 16), uint32_t, unsigned long long>::type;
+        depolarize_row<Mask>(d, r, elo, ehi, episode, attempt, thresh, key, first_q, x0, z0, x1, z1);
         s.x0 |= x0 & ~occ0;
         s.z0 |= z0 & ~occ0;
         s.x1 |= x1 & ~occ1;

@@ -180,8 +180,11 @@ step_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, const int
   }
 }
 
+#ifndef TC_RESET_MIN_CTAS
+#define TC_RESET_MIN_CTAS 5   /* the sampler is ALU-bound (profiles/r02_ncu_reset_d7.txt): 40 warps per SM instead of 24 */
+#endif
 template <int G>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, TC_RESET_MIN_CTAS)
 reset_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint8_t* __restrict__ gs,
              uint8_t* __restrict__ status, const uint32_t* __restrict__ p_thresh, uint32_t* __restrict__ episode,
              const int64_t* __restrict__ idx, int64_t n_idx, int mode, int n_fixed, uint2 key, int64_t env_base,
@@ -849,8 +852,9 @@ int tc_host_actor_step(const tc_host_step* s) {
   if (!s || bad_d(s->d) || s->n < 0) return -1;
   if (s->state_mode < 0 || s->state_mode > 2) return -1;
   if (s->n == 0) return 0;
-  if (!s->h_actions || !s->d_actions || !s->d_stage || !s->h_stage || !s->h2d_stream || !s->compute_stream ||
-      !s->d2h_stream || !s->ev_actions || !s->ev_compute || !s->ev_result || (s->state_mode && !s->ev_unpacked))
+  // (a NULL stream handle is the legacy default stream, which is what torch's default current stream is)
+  if (!s->h_actions || !s->d_actions || !s->d_stage || !s->h_stage || !s->ev_actions || !s->ev_compute ||
+      !s->ev_result || (s->state_mode && !s->ev_unpacked))
     return -1;
   if ((s->o_reward & 3) || (s->o_counts & 3) || (s->o_state & 15)) return -1;
   cudaStream_t h2d = (cudaStream_t)s->h2d_stream, cs = (cudaStream_t)s->compute_stream, d2h = (cudaStream_t)s->d2h_stream;
