@@ -82,8 +82,18 @@ struct PerspCfg {
   // warp per env spends its time on per-env setup and on expanding mostly empty tiles.  persp_write_group_kernel
   // gives a warp kGroup CONSECUTIVE envs instead: their outputs are adjacent in memory, so they are written as ONE bit
   // stream (one head / tail, full tiles in between) from kGroup plane tables.
-  static constexpr int kGroup = D == 3 ? 16 : (D == 4 ? 8 : (D == 5 ? 4 : 1));
-  static constexpr int kLanesPerEnv = D <= 4 ? 4 : 8;                       // load phase: lane = slot * kLanesPerEnv + row
+#ifndef TC_GROUP_D3
+#define TC_GROUP_D3 16
+#endif
+#ifndef TC_GROUP_D4
+#define TC_GROUP_D4 8
+#endif
+#ifndef TC_GROUP_D5
+#define TC_GROUP_D5 4
+#endif
+  static constexpr int kGroup = D == 3 ? TC_GROUP_D3 : (D == 4 ? TC_GROUP_D4 : (D == 5 ? TC_GROUP_D5 : 1));
+  // load phase: lane = slot * kLanesPerEnv + row; 4 lanes per env where the rows fit (d <= 4) and the group is large
+  static constexpr int kLanesPerEnv = (D <= 4 && kGroup >= 8) ? 4 : (kGroup >= 4 ? 8 : (kGroup == 2 ? 16 : 32));
   static constexpr int kLoadRounds = kGroup * kLanesPerEnv > 32 ? kGroup * kLanesPerEnv / 32 : 1;
   static constexpr int kTabBytes = kPlane ? kGroup * 4 * D * D * 8 : 4 * 2 * D * (int)sizeof(TabT);
   static constexpr int kPosBytes = ((kGroup * kPMax + 2) * 2 + 15) & ~15;
@@ -564,7 +574,7 @@ persp_write_group_kernel(const uint32_t* __restrict__ syn, const int32_t* __rest
       if (e0 + s >= n) break;                    // warp-uniform
       uint32_t m0, m1;
       persp_masks<32>(kFull, D, lane, v, pl, m0, m1);
-      const int P = gsum<32>(kFull, __popc(m0) + __popc(m1));
+      const int P = __reduce_add_sync(kFull, __popc(m0) + __popc(m1));      // redux.sync: one instruction
       if (lane == 0) offsets[e0 + s] = off + ktrue;
       ktrue += P;
       if (P == 0) continue;
