@@ -30,3 +30,14 @@ tail -2 gpurun_out/ncu_reset.log
 timeout 300 python scripts/kernel_table.py --ds 5,7,9 --scale 4 > gpurun_out/kernel_table_4M.jsonl 2> gpurun_out/kernel_table.err
 grep -i "reset\|actor_pre" gpurun_out/kernel_table_4M.jsonl | cut -c1-200
 timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/bench_20.json 2>gpurun_out/bench_20.err; cut -c1-200 gpurun_out/bench_20.json
+# group-writer sizes (variants built with -DTC_GROUP_D{3,4,5}=K); default build = 16 / 8 / 4
+for spec in "3 g3_8" "3 g3_32" "4 g4_4" "4 g4_16" "5 g5_2" "5 g5_8"; do
+  set -- $spec
+  if [ -f toric_rl_decoder_b200/variants/$2.so ]; then
+    echo -n "$2 " >> gpurun_out/group_variants.txt
+    TORIC_B200_LIB=$PWD/toric_rl_decoder_b200/variants/$2.so timeout 200 python bench.py --d $1 --no-cpu-baseline --no-e2e --steps 100 2>/dev/null | python -c "
+import json,sys
+j=json.loads(sys.stdin.read()); r=j['roofline']; print('d', j['config']['d'], 'ms/step %.4f writer %.4f ms %.0f GB/s'%(j['ms_per_step'], r['kernel_ms'], r['achieved']))" >> gpurun_out/group_variants.txt
+  fi
+done
+cat gpurun_out/group_variants.txt
