@@ -16,7 +16,7 @@ except Exception as e: print('bench parse failed', e)
 PY
 tail -3 gpurun_out/bench.err
 timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; cut -c1-250 gpurun_out/bench_ref.json
-for v in "" reset3 reset4; do
+for v in "" reset3 reset4 resetD; do
   if [ -n "$v" ]; then export TORIC_B200_LIB=$PWD/toric_rl_decoder_b200/variants/$v.so; else unset TORIC_B200_LIB; fi
   for args in "7 0.1" "7 0.0005" "5 0.1" "9 0.1" "25 0.1"; do
     echo -n "variant=${v:-default} " >> gpurun_out/reset_variants.txt

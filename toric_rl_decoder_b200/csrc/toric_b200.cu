@@ -183,12 +183,14 @@ step_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, const int
 #ifndef TC_RESET_MIN_CTAS
 #define TC_RESET_MIN_CTAS 5   /* the sampler is ALU-bound (profiles/r02_ncu_reset_d7.txt): 40 warps per SM instead of 24 */
 #endif
-template <int G>
+// D is a compile-time lattice size: the sampler (inlined) then has constant slot counts, masks and call counts --
+// the kernel is bound by integer instruction issue (profiles/r02_ncu_reset_d7*.txt), so this is where its time goes.
+template <int G, int D>
 __global__ void __launch_bounds__(kThreads, TC_RESET_MIN_CTAS)
 reset_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint8_t* __restrict__ gs,
              uint8_t* __restrict__ status, const uint32_t* __restrict__ p_thresh, uint32_t* __restrict__ episode,
-             const int64_t* __restrict__ idx, int64_t n_idx, int mode, int n_fixed, uint2 key, int64_t env_base,
-             int d) {
+             const int64_t* __restrict__ idx, int64_t n_idx, int mode, int n_fixed, uint2 key, int64_t env_base) {
+  constexpr int d = D;
   const uint32_t gmask = group_mask<G>();
   const int r = threadIdx.x & (G - 1);
   const int64_t k = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
@@ -703,9 +705,20 @@ int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, cons
   if (base_mode < 0 || base_mode > 2 || n_fixed < 0 || (base_mode != 0 && n_fixed == 0)) return -1;
   if (n_idx == 0) return 0;
   if (!qubits || !syn || !p_thresh || !episode) return -1;
-  TC_DISPATCH_G(d, (reset_kernel<G><<<grid_for(n_idx * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
-                       qubits, syn, gs, status, p_thresh, episode, idx, n_idx, mode, n_fixed, make_key(seed),
-                       env_base, d)));
+  switch (d) {
+#define TC_CASE(D)                                                                                              \
+  case D: {                                                                                                     \
+    constexpr int G = D <= 8 ? 8 : (D <= 16 ? 16 : 32);                                                         \
+    reset_kernel<G, D><<<grid_for(n_idx * G, kThreads), kThreads, 0, (cudaStream_t)stream>>>(                   \
+        qubits, syn, gs, status, p_thresh, episode, idx, n_idx, mode, n_fixed, make_key(seed), env_base);       \
+  } break;
+    TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8) TC_CASE(9) TC_CASE(10)
+    TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16) TC_CASE(17) TC_CASE(18)
+    TC_CASE(19) TC_CASE(20) TC_CASE(21) TC_CASE(22) TC_CASE(23) TC_CASE(24) TC_CASE(25) TC_CASE(26)
+    TC_CASE(27) TC_CASE(28) TC_CASE(29) TC_CASE(30) TC_CASE(31) TC_CASE(32)
+#undef TC_CASE
+    default: return -1;
+  }
   return launch_status();
 }
 
