@@ -167,9 +167,11 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
  *   h2d stream:      actions -> d_actions;                                  record ev_actions
  *   compute stream:  wait ev_actions [, ev_unpacked_prev]; tc_actor_pre (results written straight into d_stage);
  *                    record ev_compute; tc_persp_write_as
- *   d2h stream:      wait ev_compute; new states -> d_stage + o_state (state_mode 1: tc_unpack_state, 2:
- *                    tc_state_rows, 0: none); record ev_unpacked; d_stage -> h_stage; record ev_result
- * so the step's results, final before the perspective writer runs, cross PCIe underneath the writer.  The caller
+ *   d2h stream:      wait ev_compute; state_mode 1: tc_unpack_state -> d_stage + o_state (state_mode 2, the
+ *                    tc_state_rows format, is written by the step kernel itself; 0: no states); record ev_unpacked;
+ *                    d_stage -> h_stage; record ev_result
+ * so the step's results, final before the perspective writer runs, cross PCIe underneath the writer (give the d2h
+ * stream a higher priority than the compute stream: its work must not queue behind the writer's CTAs).  The caller
  * waits on ev_result (cudaEventSynchronize) before it reads h_stage.  Streams and events are the caller's
  * (cudaStream_t / cudaEvent_t as void*); the library creates nothing.  d_stage / h_stage layout: float32 reward [n]
  * at o_reward, int32 counts [n] at o_counts, uint8 terminal [n] at o_term, states at o_state (16-byte aligned).

@@ -392,7 +392,7 @@ def test_single_pass_step_equals_three_kernel_step(pkg, d, n, steps):
         if t % 5 == 0 or t == steps - 1:
             for x, y in zip(a.perspective_views(), b.perspective_views()):
                 assert torch.equal(x, y), t
-    assert a.read_counters()["episodes"] > 0 or n < 10
+    assert a.read_counters()["episodes"] > 0 or steps <= 10 or n < 10
 
 
 @pytest.mark.parametrize("d,n,steps,single_pass", ((7, 1500, 400, False), (7, 40000, 120, False), (5, 300, 400, False),

@@ -46,6 +46,7 @@ struct ActorArgs {
   int64_t env_base;
   int64_t n;
   int flags, max_steps, mode, n_fixed, d;
+  uint8_t* state_rows;   // nullable: the new states as lattice-row bitmasks (tc_state_rows layout), written by the step
 };
 
 constexpr uint32_t kDescAggregate = 1, kDescPrefix = 2;

@@ -83,10 +83,10 @@ struct PerspCfg {
   // gives a warp kGroup CONSECUTIVE envs instead: their outputs are adjacent in memory, so they are written as ONE bit
   // stream (one head / tail, full tiles in between) from kGroup plane tables.
 #ifndef TC_GROUP_D3
-#define TC_GROUP_D3 16
+#define TC_GROUP_D3 8
 #endif
 #ifndef TC_GROUP_D4
-#define TC_GROUP_D4 8
+#define TC_GROUP_D4 4
 #endif
 #ifndef TC_GROUP_D5
 #define TC_GROUP_D5 4

@@ -419,6 +419,15 @@ __global__ void __launch_bounds__(kThreads, TC_ACTOR_MIN_CTAS) actor_step_kernel
   if (valid) {
     store_qubits<G>(a.qubits, e, d, r, s);
     store_syn<G>(a.syn, e, d, r, s);
+    if (a.state_rows && r < d) {          // host-buffer step: the download format comes straight from the step kernel
+      const int nb = (d + 7) >> 3;
+      uint8_t* rv = a.state_rows + (e * 2 * d + r) * nb;
+      uint8_t* rp = rv + (int64_t)d * nb;
+      for (int b = 0; b < nb; ++b) {
+        rv[b] = (uint8_t)(s.v >> (8 * b));
+        rp[b] = (uint8_t)(s.pl >> (8 * b));
+      }
+    }
   }
   if (lead) {
     a.steps[e] = stp;
@@ -621,6 +630,37 @@ int fused_dispatch(const ActorArgs& a, const Workspace& w, float* out, uint8_t* 
   return launch_status();
 }
 
+// tc_actor_pre with the optional row-bitmask output of the host-buffer step
+int actor_pre_impl(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
+                 uint8_t* terminal, uint8_t* gs, uint8_t* status, int32_t* steps, uint32_t* episode,
+                 const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
+                 uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
+                 size_t workspace_bytes, int d, int64_t n, void* stream, uint8_t* state_rows) {
+  if (bad_d(d) || n < 0 || !offsets) return -1;
+  if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n == 0) {
+    cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
+    return launch_status();
+  }
+  if (!qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode || !p_thresh || !counts ||
+      !workspace)
+    return -1;
+  if ((uintptr_t)actions & 15) return -1;
+  const Workspace w = carve(workspace, d, n);
+  if (workspace_bytes < w.bytes) return -2;
+  ActorArgs a;
+  a.qubits = qubits; a.syn = syn; a.prev_syn = prev_syn; a.actions = actions; a.reward = reward;
+  a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
+  a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
+  a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
+  a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d; a.state_rows = state_rows;
+  TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kThreads, 0, st, a)));
+  launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, offsets + n,
+             counters);
+  return launch_status();
+}
+
 }  // namespace
 
 extern "C" {
@@ -801,29 +841,9 @@ int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* a
                  const uint32_t* p_thresh, int64_t* counters, int flags, int max_steps, int mode, int n_fixed,
                  uint64_t seed, int64_t env_base, int32_t* counts, int64_t* offsets, void* workspace,
                  size_t workspace_bytes, int d, int64_t n, void* stream) {
-  if (bad_d(d) || n < 0 || !offsets) return -1;
-  if (mode < 0 || mode > 2 || n_fixed < 0 || (mode != 0 && n_fixed == 0)) return -1;
-  cudaStream_t st = (cudaStream_t)stream;
-  if (n == 0) {
-    cudaMemsetAsync(offsets, 0, sizeof(int64_t), st);
-    return launch_status();
-  }
-  if (!qubits || !syn || !actions || !reward || !terminal || !gs || !steps || !episode || !p_thresh || !counts ||
-      !workspace)
-    return -1;
-  if ((uintptr_t)actions & 15) return -1;
-  const Workspace w = carve(workspace, d, n);
-  if (workspace_bytes < w.bytes) return -2;
-  ActorArgs a;
-  a.qubits = qubits; a.syn = syn; a.prev_syn = prev_syn; a.actions = actions; a.reward = reward;
-  a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
-  a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
-  a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
-  a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d;
-  TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kThreads, 0, st, a)));
-  launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, offsets + n,
-             counters);
-  return launch_status();
+  return actor_pre_impl(qubits, syn, prev_syn, actions, reward, terminal, gs, status, steps, episode, p_thresh, counters,
+                        flags, max_steps, mode, n_fixed, seed, env_base, counts, offsets, workspace, workspace_bytes, d,
+                        n, stream, nullptr);
 }
 
 int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
@@ -851,7 +871,7 @@ int tc_actor_step(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* 
     a.terminal = terminal; a.gs = gs; a.status = status; a.steps = steps; a.episode = episode;
     a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
     a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
-    a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d;
+    a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d; a.state_rows = nullptr;
     return fused_dispatch(a, w, out, pos, offsets, overflow, cap, st);
   }
   const int rc = tc_actor_pre(qubits, syn, prev_syn, actions, reward, terminal, gs, status, steps, episode,
@@ -878,18 +898,22 @@ int tc_host_actor_step(const tc_host_step* s) {
   float* reward = reinterpret_cast<float*>(s->d_stage + s->o_reward);
   int32_t* counts = reinterpret_cast<int32_t*>(s->d_stage + s->o_counts);
   uint8_t* terminal = s->d_stage + s->o_term;
-  int rc = tc_actor_pre(s->qubits, s->syn, s->prev_syn, s->d_actions, reward, terminal, s->gs, s->status, s->steps,
-                        s->episode, s->p_thresh, s->counters, s->flags, s->max_steps, s->mode, s->n_fixed, s->seed,
-                        s->env_base, counts, s->offsets, s->workspace, s->workspace_bytes, s->d, s->n, cs);
+  // state_mode 2: the step kernel itself writes the row bitmasks into the download block -- no second kernel has to
+  // find SM slots underneath the perspective writer before the results can leave
+  int rc = actor_pre_impl(s->qubits, s->syn, s->prev_syn, s->d_actions, reward, terminal, s->gs, s->status, s->steps,
+                          s->episode, s->p_thresh, s->counters, s->flags, s->max_steps, s->mode, s->n_fixed, s->seed,
+                          s->env_base, counts, s->offsets, s->workspace, s->workspace_bytes, s->d, s->n, cs,
+                          s->state_mode == 2 ? s->d_stage + s->o_state : nullptr);
   if (rc != 0) return rc;
   cudaEventRecord((cudaEvent_t)s->ev_compute, cs);
   rc = tc_persp_write_as(s->syn, s->out, s->out_dtype, s->pos, s->offsets, s->overflow, s->cap, s->workspace,
                          s->workspace_bytes, s->d, s->n, cs);
   if (rc != 0) return rc;
   cudaStreamWaitEvent(d2h, (cudaEvent_t)s->ev_compute, 0);
-  if (s->state_mode == 1) rc = tc_unpack_state(s->syn, s->d_stage + s->o_state, s->d, s->n, d2h);
-  else if (s->state_mode == 2) rc = tc_state_rows(s->syn, s->d_stage + s->o_state, s->d, s->n, d2h);
-  if (rc != 0) return rc;
+  if (s->state_mode == 1) {
+    rc = tc_unpack_state(s->syn, s->d_stage + s->o_state, s->d, s->n, d2h);
+    if (rc != 0) return rc;
+  }
   if (s->state_mode) cudaEventRecord((cudaEvent_t)s->ev_unpacked, d2h);
   cudaMemcpyAsync(s->h_stage, s->d_stage, s->stage_bytes, cudaMemcpyDeviceToHost, d2h);
   cudaEventRecord((cudaEvent_t)s->ev_result, d2h);

@@ -94,8 +94,9 @@ class HostActorPipeline:
         self.states = states
         n, d = engine.n, engine.d
         dev = engine.device
-        self.h2d_stream = torch.cuda.Stream(device=dev)
-        self.d2h_stream = torch.cuda.Stream(device=dev)
+        # high priority: the upload and the result download must not queue behind the perspective writer's CTAs
+        self.h2d_stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.d2h_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.o_reward = 0
         self.o_counts = 4 * n
         self.o_term = 8 * n
