@@ -51,7 +51,7 @@ namespace tc {
 #define TC_WRITE_WARPS 2
 #endif
 constexpr int kTileBytes = 4096 * TC_TILE_WPL; // staging tile: 32 lanes x TC_TILE_WPL stream words of float32 output
-constexpr int kStageBufs = TC_STAGE_BUFS;      // staging tiles per warp (1: wait for the TMA read before refill)
+constexpr int kStageBufsDefault = TC_STAGE_BUFS;   // staging tiles per warp (1: wait for the TMA read before refill)
 
 // Output element types.  The stream is 0/1 valued, so every type is exact; float32 is the reference's
 // (`.type('torch.Tensor')`, src/numba/util_actor.py:39), the narrower ones feed a bf16/fp16-autocast or
@@ -100,6 +100,9 @@ struct PerspCfg {
   static constexpr int kAuxBytes = kPlane ? 4 * 16 * 4 : 0;      // plane path: the 4 x d base rows, doubled
   static constexpr int kCandBytes = kPlane ? ((2 * D * D * 8 + 127) & ~127) : 0;   // per-CTA candidate table
   // per-warp shared memory: [stage tiles][tab / planes][pos list][aux]
+  // d=3: the writer is bound by per-env set-up latency, not by the store stream -- one staging tile per warp buys 25
+  // instead of 16 resident warps per SM (+19 %, profiles/r02_group_writer_sizes.txt); everywhere else two tiles win
+  static constexpr int kStageBufs = D == 3 ? 1 : kStageBufsDefault;
   static constexpr int kWarpBytes = kStageBufs * kTileBytes + ((kTabBytes + 15) & ~15) + kPosBytes + kAuxBytes;
   static constexpr int kSmemBytes = kCandBytes + kWarps * kWarpBytes;
 };
@@ -166,7 +169,7 @@ struct WriterCtx {
     using Cfg = PerspCfg<D>;
     unsigned char* wb = smem + Cfg::kCandBytes + warp * Cfg::kWarpBytes;
     stage = reinterpret_cast<OutT*>(wb);
-    tab_raw = wb + kStageBufs * kTileBytes;
+    tab_raw = wb + Cfg::kStageBufs * kTileBytes;
     sp = reinterpret_cast<uint16_t*>(tab_raw + ((Cfg::kTabBytes + 15) & ~15));
     aux = reinterpret_cast<unsigned char*>(sp) + Cfg::kPosBytes;
     cand = reinterpret_cast<const uint2*>(smem);
@@ -424,6 +427,7 @@ __device__ __forceinline__ void stream_tiles(const WriterCtx<D, OutT>& cx, int P
     uint32_t word[kWordsPerLane];
 #pragma unroll
     for (int u = 0; u < kWordsPerLane; ++u) word[u] = assemble(32 * (kWordsPerLane * t + u) + lane);
+    constexpr int kStageBufs = Cfg::kStageBufs;
     OutT* st = stage + (ring % kStageBufs) * kTileElems;
     if (ring >= kStageBufs) {                  // the TMA engine must have read the tile pushed kStageBufs ago
       if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(kStageBufs - 1) : "memory");
