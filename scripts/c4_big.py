@@ -8,8 +8,8 @@ Prints one JSON line per p with the failure counts next to both reference runs
 With --d 5 the same sweep on the second lattice size the reference published (results/evaluation_size_5.txt,
 network/converged/Size_5_NN_11_17_Mar_2020_22_33_59.pt, q = 3 forced errors).
 
-  python scripts/c4_big.py [--d 7|5] [--scale 1.0] [--n 10000000]
-  torchrun --nproc-per-node 8 ... scripts/c4_big.py --n 10000000      # episodes sharded over the ranks by global index,
+  python scripts/c4_big.py [--d 7|5] [--scale 1.0] [--count 10000000]
+  torchrun --nproc-per-node 8 ... scripts/c4_big.py --count 10000000      # episodes sharded over the ranks by global index,
                                                                       # sums all-reduced (evaluation._evaluate_one_p)
 """
 import argparse
@@ -41,8 +41,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--d", type=int, default=7, choices=(5, 7))
-    ap.add_argument("--n", type=int, default=0, help="syndromes per p (overrides the built-in sizes)")
-    ap.add_argument("--n-high-p", type=int, default=0, help="syndromes at p = 0.05 (default: --n)")
+    ap.add_argument("--count", type=int, default=0, help="syndromes per p (overrides the built-in sizes)")
+    ap.add_argument("--count-high-p", type=int, default=0, help="syndromes at p = 0.05 (default: --count)")
     a = ap.parse_args()
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -57,8 +57,8 @@ def main():
     torch.backends.cudnn.allow_tf32 = True
     torch.backends.cuda.matmul.allow_tf32 = True
     cfg = {"size": d, "min_qubit_errors": 0, "p_error": 0.1}
-    if a.n:
-        sizes = tuple((p, (a.n_high_p or a.n) if p >= 0.05 else a.n) for p, _ in sizes)
+    if a.count:
+        sizes = tuple((p, (a.count_high_p or a.count) if p >= 0.05 else a.count) for p, _ in sizes)
     for p, n in sizes:
         n = max(1024, int(n * a.scale))
         t0 = time.perf_counter()

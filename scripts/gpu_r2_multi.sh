@@ -18,7 +18,7 @@ tail -2 gpurun_out/bench_n$N.err
 timeout 900 $RUN scripts/c5_sharded.py > gpurun_out/c5_n$N.jsonl 2> gpurun_out/c5_n$N.err; echo "c5 rc=$?"
 cut -c1-260 gpurun_out/c5_n$N.jsonl; tail -2 gpurun_out/c5_n$N.err
 if [ "$C4N" != "0" ]; then
-  timeout 1500 $RUN scripts/c4_big.py --n $C4N --n-high-p $C4H > gpurun_out/c4_n$N.jsonl 2> gpurun_out/c4_n$N.err; echo "c4 rc=$?"
+  timeout 1500 $RUN scripts/c4_big.py --count $C4N --count-high-p $C4H > gpurun_out/c4_n$N.jsonl 2> gpurun_out/c4_n$N.err; echo "c4 rc=$?"
   cut -c1-420 gpurun_out/c4_n$N.jsonl; tail -2 gpurun_out/c4_n$N.err
 fi
 if [ "$C3S" != "0" ]; then

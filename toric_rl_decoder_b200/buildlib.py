@@ -11,7 +11,7 @@ CSRC = os.path.join(PKG_DIR, "csrc")
 # TORIC_B200_LIB selects another build of the same sources (kernel-variant experiments); default: in-tree
 LIB_PATH = os.environ.get("TORIC_B200_LIB") or os.path.join(PKG_DIR, "libtoric_b200.so")
 SOURCES = [os.path.join(CSRC, "toric_b200.cu")]
-HEADERS = [os.path.join(CSRC, h) for h in ("common.cuh", "state_kernels.cuh", "sampler.cuh", "persp_write.cuh", "fused_step.cuh",
+HEADERS = [os.path.join(CSRC, h) for h in ("common.cuh", "state_kernels.cuh", "sampler.cuh", "reset_env.cuh", "persp_write.cuh", "fused_step.cuh",
                                             "policy_kernels.cuh")] + \
           [os.path.join(os.path.dirname(PKG_DIR), "include", "toric_b200.h")]
 

@@ -1,0 +1,117 @@
+// K1 for small lattices (d <= 8), depolarizing mode: ONE THREAD PER ENVIRONMENT.
+//
+// reset_kernel gives an env a group of 8 lanes (lane = lattice row).  ncu (profiles/r02_ncu_reset_d7*.txt) shows that
+// kernel bound by integer instruction issue with 20 of 32 threads active on average: 7 of 8 lanes hold a row, every
+// group-uniform quantity is computed 8 times, the Pauli-code loop runs for the slowest row of the warp.  Here a thread
+// draws all 2d rows of its env itself (same draw numbering -- csrc/sampler.cuh:depolarize_row -- so the result is
+// bit-identical), keeps the four qubit planes as 64-bit words (row r at bits [r*d, r*d + d), d*d <= 64), computes the
+// syndrome with four shifts per plane, and the CTA writes the packed rows out through shared memory so that global
+// stores stay coalesced although consecutive threads own consecutive envs.
+#pragma once
+#include "sampler.cuh"
+
+namespace tc {
+
+constexpr int kResetEnvThreads = 128;
+
+template <int D>
+__global__ void __launch_bounds__(kResetEnvThreads)
+reset_env_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint8_t* __restrict__ gs,
+                 uint8_t* __restrict__ status, const uint32_t* __restrict__ p_thresh, uint32_t* __restrict__ episode,
+                 const int64_t* __restrict__ idx, int64_t n_idx, int one_draw, uint2 key, int64_t env_base) {
+  static_assert(D >= kMinD && D <= 8, "one plane must fit 64 bits");
+  constexpr int DD = D * D;
+  constexpr int nq = 2 * DD;
+  constexpr unsigned long long kAll = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
+  constexpr uint32_t kRow = (1u << D) - 1u;
+  constexpr int kStride = 6 * D + 1;             // odd: thread-major staging writes are bank-conflict free
+  __shared__ uint32_t stage[kResetEnvThreads * kStride];
+  unsigned long long col0 = 0;                   // column 0 of every row
+#pragma unroll
+  for (int i = 0; i < D; ++i) col0 |= 1ull << (i * D);
+  const unsigned long long colL = col0 << (D - 1);
+
+  const int64_t k0 = (int64_t)blockIdx.x * kResetEnvThreads;
+  const int64_t k = k0 + threadIdx.x;
+  const bool valid = k < n_idx;
+  const int64_t e = valid ? (idx ? idx[k] : k) : 0;
+  unsigned long long x0 = 0, x1 = 0, z0 = 0, z1 = 0, v = 0, pl = 0;
+  uint32_t ep = 0;
+  uint8_t st = 0;
+  if (valid) {
+    ep = episode[e];
+    const uint32_t thresh = p_thresh[e];
+    const uint64_t env_id = (uint64_t)(env_base + e);
+    const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
+    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
+    if (conditioned && thresh == 0u) {
+      st = kStatusResetGaveUp;                   // p == 0: nothing to condition on (sampler.cuh)
+    } else {
+      uint32_t attempt = 0;
+      while (true) {
+        int first_q = -1;
+        if (conditioned) {
+          const uint4 rf = philox4x32_10(make_uint4(elo, ehi, ep, kDomFirst | attempt), key);
+          first_q = first_error_index(thresh, nq, rf.x, rf.y);
+        }
+        x0 = x1 = z0 = z1 = 0;
+#pragma unroll 1
+        for (int row = 0; row < D; ++row) {
+          uint32_t rx0, rz0, rx1, rz1;
+          depolarize_row<uint32_t>(D, row, elo, ehi, ep, attempt, thresh, key, first_q, rx0, rz0, rx1, rz1);
+          const int sh = row * D;
+          x0 |= (unsigned long long)rx0 << sh;
+          z0 |= (unsigned long long)rz0 << sh;
+          x1 |= (unsigned long long)rx1 << sh;
+          z1 |= (unsigned long long)rz1 << sh;
+        }
+        // createSyndromOpt (ToricCode.py:168-199) on whole planes:
+        //   V[i,j]  = z0[i,j] ^ z0[i-1,j] ^ z1[i,j] ^ z1[i,j-1];   Pl[i,j] = x0[i,j] ^ x0[i,j+1] ^ x1[i,j] ^ x1[i+1,j]
+        const unsigned long long z0_up = ((z0 << D) | (z0 >> (DD - D))) & kAll;               // row i <- row i-1
+        const unsigned long long z1_lf = (((z1 << 1) & ~col0) | ((z1 >> (D - 1)) & col0)) & kAll;   // col j <- col j-1
+        const unsigned long long x0_rt = ((x0 >> 1) & ~colL) | ((x0 << (D - 1)) & colL);      // col j <- col j+1
+        const unsigned long long x1_dn = ((x1 >> D) | (x1 << (DD - D))) & kAll;               // row i <- row i+1
+        v = z0 ^ z0_up ^ z1 ^ z1_lf;
+        pl = x0 ^ x0_rt ^ x1 ^ x1_dn;
+        ++attempt;
+        if ((v | pl) != 0ull || one_draw) break;
+        if (attempt >= kMaxAttempts) { st = kStatusResetGaveUp; break; }
+      }
+    }
+  }
+  // rows of this env in the HBM layout: qubits [4][d] then syn [2][d]
+  uint32_t* mine = stage + threadIdx.x * kStride;
+#pragma unroll
+  for (int r = 0; r < D; ++r) {
+    mine[0 * D + r] = (uint32_t)(x0 >> (r * D)) & kRow;
+    mine[1 * D + r] = (uint32_t)(x1 >> (r * D)) & kRow;
+    mine[2 * D + r] = (uint32_t)(z0 >> (r * D)) & kRow;
+    mine[3 * D + r] = (uint32_t)(z1 >> (r * D)) & kRow;
+    mine[4 * D + r] = (uint32_t)(v >> (r * D)) & kRow;
+    mine[5 * D + r] = (uint32_t)(pl >> (r * D)) & kRow;
+  }
+  __syncthreads();
+  if (idx == nullptr) {                          // the CTA's envs are consecutive: coalesced copies
+    const int64_t rest = n_idx - k0;
+    const int cnt = rest < kResetEnvThreads ? (int)rest : kResetEnvThreads;
+    uint32_t* gq = qubits + k0 * 4 * D;
+    for (int w = threadIdx.x; w < cnt * 4 * D; w += kResetEnvThreads) gq[w] = stage[(w / (4 * D)) * kStride + w % (4 * D)];
+    uint32_t* gsyn = syn + k0 * 2 * D;
+    for (int w = threadIdx.x; w < cnt * 2 * D; w += kResetEnvThreads)
+      gsyn[w] = stage[(w / (2 * D)) * kStride + 4 * D + w % (2 * D)];
+  } else if (valid) {                            // listed envs (resetTerminalEnvs): scattered, written per thread
+    uint32_t* gq = qubits + e * 4 * D;
+    uint32_t* gsyn = syn + e * 2 * D;
+#pragma unroll
+    for (int w = 0; w < 4 * D; ++w) gq[w] = mine[w];
+#pragma unroll
+    for (int w = 0; w < 2 * D; ++w) gsyn[w] = mine[4 * D + w];
+  }
+  if (valid) {
+    episode[e] = ep + 1;
+    if (gs) gs[e] = 1;
+    if (status && st) status[e] |= st;
+  }
+}
+
+}  // namespace tc

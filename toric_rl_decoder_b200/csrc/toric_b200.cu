@@ -8,6 +8,7 @@
 #include "fused_step.cuh"
 #include "persp_write.cuh"
 #include "policy_kernels.cuh"
+#include "reset_env.cuh"
 #include "state_kernels.cuh"
 
 namespace tc {
@@ -745,6 +746,23 @@ int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, cons
   if (base_mode < 0 || base_mode > 2 || n_fixed < 0 || (base_mode != 0 && n_fixed == 0)) return -1;
   if (n_idx == 0) return 0;
   if (!qubits || !syn || !p_thresh || !episode) return -1;
+#ifndef TC_NO_RESET_ENV_KERNEL
+  if (base_mode == 0 && d <= 8) {     // small lattices, depolarizing: one thread per env (csrc/reset_env.cuh)
+    const int one_draw = (mode & TC_SAMPLE_ONE_DRAW) ? 1 : 0;
+    const unsigned grid = grid_for(n_idx, kResetEnvThreads);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (d) {
+#define TC_CASE(D)                                                                                                    \
+  case D:                                                                                                             \
+    reset_env_kernel<D><<<grid, kResetEnvThreads, 0, st>>>(qubits, syn, gs, status, p_thresh, episode, idx, n_idx,   \
+                                                            one_draw, make_key(seed), env_base);                      \
+    break;
+      TC_CASE(3) TC_CASE(4) TC_CASE(5) TC_CASE(6) TC_CASE(7) TC_CASE(8)
+#undef TC_CASE
+    }
+    return launch_status();
+  }
+#endif
   switch (d) {
 #define TC_CASE(D)                                                                                              \
   case D: {                                                                                                     \
