@@ -24,8 +24,10 @@ reset_env_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint
   constexpr int nq = 2 * DD;
   constexpr unsigned long long kAll = DD >= 64 ? ~0ull : ((1ull << (DD & 63)) - 1ull);
   constexpr uint32_t kRow = (1u << D) - 1u;
-  constexpr int kStride = 6 * D + 1;             // odd: thread-major staging writes are bank-conflict free
-  __shared__ uint32_t stage[kResetEnvThreads * kStride];
+  // staging in the HBM layout itself (env-major, dense): the copy-out is then a linear, coalesced memcpy without any
+  // index arithmetic; the thread-major staging stores take a 4-way bank conflict (stride 4d / 2d words), which is cheap
+  __shared__ uint32_t stage_q[kResetEnvThreads * 4 * D];
+  __shared__ uint32_t stage_s[kResetEnvThreads * 2 * D];
   unsigned long long col0 = 0;                   // column 0 of every row
 #pragma unroll
   for (int i = 0; i < D; ++i) col0 |= 1ull << (i * D);
@@ -79,33 +81,33 @@ reset_env_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint
       }
     }
   }
-  // rows of this env in the HBM layout: qubits [4][d] then syn [2][d]
-  uint32_t* mine = stage + threadIdx.x * kStride;
+  // rows of this env in the HBM layout: qubits [4][d], syn [2][d]
+  uint32_t* mq = stage_q + threadIdx.x * 4 * D;
+  uint32_t* ms = stage_s + threadIdx.x * 2 * D;
 #pragma unroll
   for (int r = 0; r < D; ++r) {
-    mine[0 * D + r] = (uint32_t)(x0 >> (r * D)) & kRow;
-    mine[1 * D + r] = (uint32_t)(x1 >> (r * D)) & kRow;
-    mine[2 * D + r] = (uint32_t)(z0 >> (r * D)) & kRow;
-    mine[3 * D + r] = (uint32_t)(z1 >> (r * D)) & kRow;
-    mine[4 * D + r] = (uint32_t)(v >> (r * D)) & kRow;
-    mine[5 * D + r] = (uint32_t)(pl >> (r * D)) & kRow;
+    mq[0 * D + r] = (uint32_t)(x0 >> (r * D)) & kRow;
+    mq[1 * D + r] = (uint32_t)(x1 >> (r * D)) & kRow;
+    mq[2 * D + r] = (uint32_t)(z0 >> (r * D)) & kRow;
+    mq[3 * D + r] = (uint32_t)(z1 >> (r * D)) & kRow;
+    ms[0 * D + r] = (uint32_t)(v >> (r * D)) & kRow;
+    ms[1 * D + r] = (uint32_t)(pl >> (r * D)) & kRow;
   }
   __syncthreads();
-  if (idx == nullptr) {                          // the CTA's envs are consecutive: coalesced copies
+  if (idx == nullptr) {                          // the CTA's envs are consecutive: linear coalesced copies
     const int64_t rest = n_idx - k0;
     const int cnt = rest < kResetEnvThreads ? (int)rest : kResetEnvThreads;
     uint32_t* gq = qubits + k0 * 4 * D;
-    for (int w = threadIdx.x; w < cnt * 4 * D; w += kResetEnvThreads) gq[w] = stage[(w / (4 * D)) * kStride + w % (4 * D)];
+    for (int w = threadIdx.x; w < cnt * 4 * D; w += kResetEnvThreads) gq[w] = stage_q[w];
     uint32_t* gsyn = syn + k0 * 2 * D;
-    for (int w = threadIdx.x; w < cnt * 2 * D; w += kResetEnvThreads)
-      gsyn[w] = stage[(w / (2 * D)) * kStride + 4 * D + w % (2 * D)];
+    for (int w = threadIdx.x; w < cnt * 2 * D; w += kResetEnvThreads) gsyn[w] = stage_s[w];
   } else if (valid) {                            // listed envs (resetTerminalEnvs): scattered, written per thread
     uint32_t* gq = qubits + e * 4 * D;
     uint32_t* gsyn = syn + e * 2 * D;
 #pragma unroll
-    for (int w = 0; w < 4 * D; ++w) gq[w] = mine[w];
+    for (int w = 0; w < 4 * D; ++w) gq[w] = mq[w];
 #pragma unroll
-    for (int w = 0; w < 2 * D; ++w) gsyn[w] = mine[4 * D + w];
+    for (int w = 0; w < 2 * D; ++w) gsyn[w] = ms[w];
   }
   if (valid) {
     episode[e] = ep + 1;
