@@ -157,6 +157,10 @@ def test_envset_envs_views(pkg):
     # state setter + reset of one env
     v.state = np.zeros((2, d, d), dtype=int)
     assert v.isTerminalState(v.state)
+    st, r, term, _ = v.step([0, 1, 1, 3])                    # inconsistent pair: reward vs the assigned (empty) state
+    q_v, ns_v, ro_v, to_v = O.step(qo, np.zeros((2, d, d), dtype=np.int64), [0, 1, 1, 3])
+    assert (st == ns_v).all() and r == ro_v and term == to_v
+    qo = q_v
     s3 = es.envs[3].reset(p_error=0.3)
     assert s3.any() and (O.syndrome(es.envs[3].qubit_matrix) == s3).all() and abs(es.envs[3].p_error - 0.3) < 1e-9
     now = es.engine.get_qubits().cpu().numpy().astype(np.int64)
@@ -187,6 +191,23 @@ def test_single_env_api(pkg):
     s = env.reset(p_error=0.2)
     assert s.shape == (2, 5, 5) and s.any() and env.ground_state is True
     assert (O.syndrome(env.qubit_matrix) == s).all()
+    # an INCONSISTENT pair, as plain attribute assignment allows in the reference (results/small_p_error_test.py:119-120):
+    # the step's reward is taken against the assigned state, the new state is recomputed from the qubits (ToricCode.py:83-86)
+    q = g["qubits"][2].astype(np.int64)
+    env.qubit_matrix = q
+    fake = np.zeros((2, 5, 5), dtype=int)
+    fake[0, 1, 1] = fake[1, 3, 2] = fake[1, 0, 4] = 1
+    env.state = fake
+    assert (env.state == fake).all()
+    gs_before = env.ground_state
+    a = [1, 2, 3, 2]
+    st, r, term, _ = env.step(a)
+    q1, ns, ro, to = O.step(q, fake, a)
+    assert (st == ns).all() and r == ro and term == to and (env.qubit_matrix == q1).all()
+    assert env.ground_state == gs_before                     # assignment and step leave the sticky flag alone
+    st, r, term, _ = env.step([0, 0, 0, 1])                  # consistent again: the incremental path
+    q2, ns2, ro2, to2 = O.step(q1, ns, [0, 0, 0, 1])
+    assert (st == ns2).all() and r == ro2 and term == to2
 
 
 @pytest.mark.parametrize("d,n", ((7, 1024), (9, 256), (4, 64), (16, 64), (17, 32), (32, 8)))

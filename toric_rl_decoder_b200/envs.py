@@ -44,6 +44,7 @@ class ToricCodeB200:
         self.rule_table = np.array([[0, 1, 2, 3], [1, 0, 3, 2], [2, 3, 0, 1], [3, 2, 1, 0]], dtype=int)
         self._eng = ToricEngine(d, 1, device=device, seed=seed, env_base=env_base, p_error=self.p_error)
         self._scratch = None      # second engine for the pure functions (createSyndromOpt, generate*Error*)
+        self._state_assigned = False   # `state` was assigned since the last step / reset (see the setter)
         self.next_state = self.state
 
     # -- attribute surface -------------------------------------------------------------------------
@@ -53,8 +54,14 @@ class ToricCodeB200:
 
     @qubit_matrix.setter
     def qubit_matrix(self, q):
-        # the reference assigns qubit_matrix and state separately; here the syndrome follows the qubits
-        self._eng.set_qubits(np.asarray(q).astype(np.uint8)[None])
+        """Mask injection.  The reference assigns `qubit_matrix` and `state` as two independent attributes
+        (results/small_p_error_test.py:119-120) and leaves `ground_state` alone; here the syndrome additionally follows
+        the qubits at once (the reference's `state` would stay stale until it is assigned or a step recomputes it) and
+        `ground_state` is, like there, not touched."""
+        e = self._eng
+        t = e._as_u8(np.asarray(q).astype(np.uint8)[None], (1, 2, e.d, e.d))
+        _lib.check(e.lib.tc_pack_qubits(_ptr(t), _ptr(e.qubits), e.d, 1, _stream(e.device)), "tc_pack_qubits")
+        e.syndrome()
 
     @property
     def state(self):
@@ -62,7 +69,12 @@ class ToricCodeB200:
 
     @state.setter
     def state(self, s):
+        """Assigning `state` may leave it INCONSISTENT with `qubit_matrix` (the reference allows it: two plain
+        attributes).  The reference's next step then takes its reward from the assigned state but recomputes the new
+        state from the qubits (ToricCode.py:83-86); the next step() here does the same instead of the incremental
+        update."""
         self._eng.set_state((np.asarray(s) != 0).astype(np.uint8)[None])
+        self._state_assigned = True
 
     @property
     def ground_state(self):
@@ -77,6 +89,7 @@ class ToricCodeB200:
         """ToricCode.reset (ToricCode.py:90-127)."""
         if p_error is not None:
             self.p_error = p_error
+        self._state_assigned = False
         self._eng.set_p_error(self.p_error)
         if self.min_qbit_errors == 0:
             self._eng.reset(mode=SAMPLE_DEPOLARIZING)
@@ -87,6 +100,14 @@ class ToricCodeB200:
     def step(self, action):
         """ToricCode.step (ToricCode.py:62-88): returns (state, reward, terminal, {})."""
         a = np.asarray(action, dtype=np.int64).reshape(1, 4)
+        if self._state_assigned:      # reward against the assigned state, new state recomputed from the qubits
+            before = int(self.state.sum())
+            self._eng.step(torch.from_numpy(a))
+            self._eng.syndrome()
+            self._state_assigned = False
+            self.next_state = self.state
+            after = int(self.next_state.sum())
+            return self.next_state, (100 if after == 0 else before - after), after == 0, {}
         reward, terminal = self._eng.step(torch.from_numpy(a))
         r = reward[0].item()
         self.next_state = self.state
@@ -177,7 +198,7 @@ class _EnvView:
         t = e._as_u8(np.asarray(codes).astype(np.uint8)[None], (1, 2, e.d, e.d))
         _lib.check(e.lib.tc_pack_qubits(_ptr(t), _ptr(q), e.d, 1, _stream(e.device)), "tc_pack_qubits")
         _lib.check(e.lib.tc_syndrome(_ptr(q), _ptr(syn), e.d, 1, _stream(e.device)), "tc_syndrome")
-        e.gs[self._i] = 1
+        # ground_state is left alone, as in the reference (plain attribute assignment)
 
     @property
     def state(self):
@@ -189,6 +210,7 @@ class _EnvView:
         e, _, syn = self._rows()
         t = e._as_u8((np.asarray(s) != 0).astype(np.uint8)[None], (1, 2, e.d, e.d))
         _lib.check(e.lib.tc_pack_state(_ptr(t), _ptr(syn), e.d, 1, _stream(e.device)), "tc_pack_state")
+        self._es._state_assigned.add(self._i)       # see ToricCodeB200.state: the next step recomputes from the qubits
 
     @property
     def ground_state(self):
@@ -210,9 +232,17 @@ class _EnvView:
         e, q, syn = self._rows()
         i = self._i
         a = torch.as_tensor(np.asarray(action, dtype=np.int32).reshape(1, 4)).to(e.device)
+        assigned = i in self._es._state_assigned
+        before = int(self.state.sum()) if assigned else 0
         _lib.check(e.lib.tc_step(_ptr(q), _ptr(syn), _ptr(a), _ptr(e.reward[i:i + 1]), _ptr(e.terminal[i:i + 1]),
                                  _ptr(e.status[i:i + 1]), e.d, 1, _stream(e.device)), "tc_step")
         e.steps[i] += 1
+        if assigned:                  # ToricCode.py:83-86: new state from the qubits, reward against the assigned one
+            self._es._state_assigned.discard(i)
+            _lib.check(e.lib.tc_syndrome(_ptr(q), _ptr(syn), e.d, 1, _stream(e.device)), "tc_syndrome")
+            st = self.state
+            after = int(st.sum())
+            return st, (100 if after == 0 else before - after), after == 0, {}
         return self.state, int(e.reward[i].item()), bool(e.terminal[i].item()), {}
 
     def evalGroundState(self):
@@ -266,6 +296,7 @@ class EnvSetB200:
         self.numpy_compat = numpy_compat
         self.engine = ToricEngine(size, self.no_envs, device=device, seed=seed, env_base=env_base, p_error=p)
         self.envs = _EnvList(self)
+        self._state_assigned = set()     # envs whose `state` was assigned through envs[i] since their last step / reset
         self.states = self._states()
 
     def _states(self):
@@ -273,6 +304,10 @@ class EnvSetB200:
         return st.cpu().numpy().astype(np.int64) if self.numpy_compat else st
 
     def _reset(self, idx):
+        if idx is None:
+            self._state_assigned.clear()
+        else:
+            self._state_assigned.difference_update(int(i) for i in np.asarray(idx).reshape(-1))
         if self.min_qbit_errors == 0:
             self.engine.reset(idx, mode=SAMPLE_DEPOLARIZING)
         else:
