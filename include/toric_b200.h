@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 4
+#define TC_ABI_VERSION 5
 #define TC_NUM_COUNTERS 16
 
 /* status bits written per env */

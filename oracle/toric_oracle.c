@@ -159,24 +159,46 @@ static void depolarize_row(uint8_t* field /* [2][d][d], written for row `row` on
       if (q < first_q) err[s] = 0;
       if (q == first_q) err[s] = 1;
     }
-  int c = ncalls - 1, pos = 16 * (nslots & 7);
-  if (pos == 0) pos = 128;
+  /* Pauli codes: 2-bit chunks of the stream behind the last slot (word-aligned), chunk 0 rejected.  Slot s first reads
+   * chunk s; the error slots whose chunk was 0 then take the chunks from index nslots on, in increasing s. */
+  int c = ncalls - 1, wi = (nslots & 7) ? ((nslots & 7) >> 1) : 4, any = 0;
+  uint8_t code[64];
+  for (int s = 0; s < nslots; ++s) { code[s] = 0; any |= err[s]; }
+  if (any) {
+    uint32_t words[4] = {0, 0, 0, 0}, cur = 0;
+    const int nwords = (nslots + 15) / 16;
+    int left;
+#define NEXT_WORD(dst)                                                                                             \
+  do {                                                                                                             \
+    if (wi == 4) {                                                                                                 \
+      ++c;                                                                                                         \
+      const uint32_t ctr_[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, base | (uint32_t)(c & 15)};   \
+      to_philox4x32_10(ctr_, key, rnd);                                                                            \
+      wi = 0;                                                                                                      \
+    }                                                                                                              \
+    (dst) = rnd[wi++];                                                                                             \
+  } while (0)
+    for (int j = 0; j < nwords; ++j) NEXT_WORD(words[j]);
+    for (int s = 0; s < nslots; ++s)
+      if (err[s]) code[s] = (uint8_t)((words[s >> 4] >> (2 * (s & 15))) & 3u);
+    left = (16 - (nslots & 15)) & 15;
+    cur = left ? (words[nwords - 1] >> (2 * (16 - left))) : 0u;
+    for (int s = 0; s < nslots; ++s) {
+      if (!err[s] || code[s]) continue;
+      uint32_t v;
+      do {
+        if (left == 0) { NEXT_WORD(cur); left = 16; }
+        v = cur & 3u;
+        cur >>= 2;
+        --left;
+      } while (v == 0);
+      code[s] = (uint8_t)v;
+    }
+#undef NEXT_WORD
+  }
   for (int s = 0; s < nslots; ++s) {
     const int m = s / d, j = s - m * d;
-    uint32_t v = 0;
-    if (err[s]) {
-      do {
-        if (pos >= 128) {
-          ++c;
-          const uint32_t ctr[4] = {(uint32_t)env_id, (uint32_t)(env_id >> 32), episode, base | (uint32_t)(c & 15)};
-          to_philox4x32_10(ctr, key, rnd);
-          pos = 0;
-        }
-        v = (rnd[pos >> 5] >> (pos & 31)) & 3u;
-        pos += 2;
-      } while (v == 0);
-    }
-    field[IDX(m, row, j)] = (uint8_t)v;           /* 0 = no error, else the Pauli code */
+    field[IDX(m, row, j)] = code[s];              /* 0 = no error, else the Pauli code */
   }
 }
 

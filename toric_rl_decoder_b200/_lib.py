@@ -54,7 +54,7 @@ SIGNATURES = {
     "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],
 }
 
-ABI_VERSION = 4
+ABI_VERSION = 5
 _lib = None
 
 

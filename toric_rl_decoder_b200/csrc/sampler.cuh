@@ -14,10 +14,11 @@
 //      2^-16) -> refined by word s%4 of call 16 + s/4:  error iff (word & 0xffff) < (T & 0xffff).
 //      Together that is exactly "a 32-bit uniform < T", the uniform's low half being drawn only when needed --
 //      8 qubits per Philox call instead of 2.
-//    * Pauli codes: the row's error qubits in increasing s take 2-bit chunks from the bit stream that starts
-//      right behind the row's last slot (bit 16*(2d%8) of call (2d-1)/8; call 2d/8 when 2d%8 == 0) and runs on
-//      through the following calls (c & 15); chunk 0 is rejected, chunk v in {1,2,3} is the Pauli code --
-//      exactly uniform, ~2.7 bits per error instead of a 32-bit word per QUBIT.
+//    * Pauli codes: 2-bit chunks of the bit stream that starts right behind the row's last slot (bit 16*(2d%8) of call
+//      (2d-1)/8; call 2d/8 when 2d%8 == 0) and runs on through the following calls (c & 15).  Chunk 0 is rejected, chunk
+//      v in {1,2,3} is the Pauli code -- exactly uniform.  Slot s first reads chunk s of the stream (positional, so the
+//      whole row is assigned bit-parallel); the error slots whose chunk was 0, in increasing s, then take the chunks from
+//      index 2d on, one after the other, until theirs is non-zero.
 //  rejection (ToricCode.py:108-117): attempts are repeated until the syndrome is non-trivial.  When
 //    T * 2d^2 < 2^32 (p * #qubits < 1: most draws would hold no error at all) the field is drawn CONDITIONED
 //    on holding at least one error -- same distribution after the rejection, O(1) attempts at any p:
@@ -59,6 +60,16 @@ __device__ __noinline__ int first_error_index(uint32_t thresh, int nq, uint32_t 
   const double u = (double)u53 * (1.0 / 9007199254740992.0);
   const double k = floor(log1p(-u * mass) / log_q);
   return k >= (double)(nq - 1) ? nq - 1 : (k > 0.0 ? (int)k : 0);
+}
+
+// bits 0, 2, 4, .. 30 of x packed into bits 0..15
+__device__ __forceinline__ uint32_t even_bits(uint32_t x) {
+  x &= 0x55555555u;
+  x = (x | (x >> 1)) & 0x33333333u;
+  x = (x | (x >> 2)) & 0x0f0f0f0fu;
+  x = (x | (x >> 4)) & 0x00ff00ffu;
+  x = (x | (x >> 8)) & 0x0000ffffu;
+  return x;
 }
 
 __device__ __forceinline__ int first_set(uint32_t m) { return __ffs((int)m) - 1; }
@@ -111,34 +122,51 @@ __device__ __forceinline__ void depolarize_row(int d, int row, uint32_t elo, uin
       err = (err & ~(clean << (m * d))) | (one << (m * d));
     }
   }
-  // Pauli codes: 2-bit chunks from the words behind the last slot (2d is even, so the stream starts on a word
-  // boundary: word (2d % 8) / 2 of the last call, or the next call when that one is full), chunk 0 rejected
-  M xs = 0, zs = 0;
+  // Pauli codes: 2-bit chunks (chunk 0 rejected, chunk v in {1,2,3} = the code) from the words behind the last slot --
+  // 2d is even, so the stream starts on a word boundary: word (2d % 8) / 2 of the last call, or the next call when that
+  // one is full.  First pass, bit-parallel: slot s reads chunk s (low bit -> plane A, high bit -> plane B); second pass:
+  // the error slots whose chunk was 0 (a quarter of them), in increasing s, take further chunks from chunk 2d on.
   int c = ncalls - 1;
   int wi = (nslots & 7) ? ((nslots & 7) >> 1) : 4;   // next word of the current call (4 = exhausted)
+  auto next_word = [&]() -> uint32_t {
+    if (wi == 4) {
+      ++c;
+      rnd = philox4x32_10(make_uint4(elo, ehi, episode, base | (uint32_t)(c & 15)), key);
+      wi = 0;
+    }
+    return word_of(rnd, wi++);
+  };
+  M pa = 0, pb = 0;
   uint32_t cur = 0;
-  int left = 0;                                  // chunks left in `cur`
-  M todo = err;
+  int left = 0;
+  if (err) {                                     // a row without errors reads nothing
+    const int nwords = (nslots + 15) >> 4;
+#pragma unroll 1
+    for (int j = 0; j < nwords; ++j) {
+      cur = next_word();
+      pa |= (M)even_bits(cur) << (16 * j);
+      pb |= (M)even_bits(cur >> 1) << (16 * j);
+    }
+    left = (16 - (nslots & 15)) & 15;            // chunks left in `cur` behind chunk 2d - 1
+    cur = left ? (cur >> (2 * (16 - left))) : 0u;
+  }
+  M xs = err & (pa ^ pb);                        // 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3}
+  M zs = err & pb;
+  M todo = err & ~(pa | pb);
   while (todo) {
     const int s = first_set(todo);
     todo &= todo - 1;
     uint32_t v;
     do {
       if (left == 0) {
-        if (wi == 4) {
-          ++c;
-          rnd = philox4x32_10(make_uint4(elo, ehi, episode, base | (uint32_t)(c & 15)), key);
-          wi = 0;
-        }
-        cur = word_of(rnd, wi);
-        ++wi;
+        cur = next_word();
         left = 16;
       }
       v = cur & 3u;
       cur >>= 2;
       --left;
     } while (v == 0u);
-    if (v != 3u) xs |= (M)1 << s;                // 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3}
+    if (v != 3u) xs |= (M)1 << s;
     if (v != 1u) zs |= (M)1 << s;
   }
   const uint32_t rm = row_mask(d);
