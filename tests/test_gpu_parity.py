@@ -271,6 +271,36 @@ def test_capacity_overflow_regenerates(pkg):
     assert (c == oc).all() and (p == op).all() and (ps == opos).all()
 
 
+@pytest.mark.parametrize("d,n", ((3, 1000), (4, 777), (5, 1234), (7, 500), (9, 300), (15, 60)))
+def test_partial_capacity_writes_the_envs_that_fit_and_nothing_else(pkg, d, n):
+    """A perspective buffer smaller than sum P (every writer form: group writer d <= 5, plane path, row path): the envs
+    whose perspectives fit are written exactly, nothing lands past the capacity, offsets are the true ones, the flag is
+    set."""
+    rng = np.random.default_rng(d * 1000 + n)
+    q = ((rng.random((n, 2, d, d)) < 0.08) * rng.integers(1, 4, (n, 2, d, d))).astype(np.uint8)
+    ref = pkg.ToricEngine(d, n)
+    ref.set_qubits(q)
+    ref.perspectives()
+    p_ref, pos_ref, c_ref, off_ref = ref.perspective_views()
+    total = int(off_ref[-1].item())
+    for cap in (total // 2 + 1, total - 1, 1):
+        eng = pkg.ToricEngine(d, n)
+        eng.set_qubits(q)
+        eng.ensure_capacity(cap + 64)
+        eng.cap = cap                                   # the library sees `cap`; 64 guard perspectives behind it
+        eng.out.view(torch.uint8).fill_(0x5a)
+        eng.pos.fill_(0x5a)
+        eng.perspectives()
+        torch.cuda.synchronize()
+        assert int(eng.overflow.item()) == 1
+        assert torch.equal(eng.offsets[:n + 1], off_ref) and torch.equal(eng.counts[:n], c_ref)
+        ends = off_ref[1:]
+        fit = int((ends <= cap).sum().item())           # offsets grow with the env index: the fitting envs are a prefix
+        kept = int(off_ref[fit].item())
+        assert torch.equal(eng.out[:kept], p_ref[:kept]) and torch.equal(eng.pos[:kept, :3], pos_ref[:kept, :3])
+        assert (eng.out[cap:].view(torch.uint8) == 0x5a).all() and (eng.pos[cap:] == 0x5a).all()
+
+
 def test_abi_argument_errors(pkg):
     from toric_rl_decoder_b200 import _lib
     lib = _lib.load()
