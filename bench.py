@@ -282,9 +282,22 @@ def run_b200(a):
         torch.cuda.synchronize()
 
     write_peak = measure_write_peak(dev)
-    for _ in range(a.warmup):
-        eng.actor_step()
+    # warm-up: the fused call, and once the split form with its event records and the device-side copy of sum P, so that
+    # nothing is used for the first time (lazy module loads, allocator growth) inside a short timed region
+    warm_ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    warm_tot = torch.zeros(1, dtype=torch.int64, device=dev)
+    for w in range(a.warmup):
+        if w == 0 and not one_kernel:
+            eng.actor_pre()
+            warm_ev[0].record()
+            eng.persp_write()
+            warm_ev[1].record()
+            warm_tot[0].copy_(eng.offsets[n], non_blocking=True)
+        else:
+            eng.actor_step()
     barrier()
+    if not one_kernel and a.warmup > 0:
+        warm_ev[0].elapsed_time(warm_ev[1])
     eng.counters.zero_()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # The step is the fused call a user makes (tc_actor_step: three back-to-back launches).  Every
