@@ -160,8 +160,7 @@ static void depolarize_row(uint8_t* field /* [2][d][d], written for row `row` on
       if (q == first_q) err[s] = 1;
     }
   /* Pauli codes: 2-bit chunks of the stream behind the last slot (word-aligned), chunk 0 rejected.  Slot s first reads
-   * chunk s; the error slots whose chunk was 0 then, in increasing s, take further chunks: first the positional chunks
-   * of the error-free slots (in slot order), then the stream from chunk index nslots on. */
+   * chunk s; the error slots whose chunk was 0 then take the chunks from index nslots on, in increasing s. */
   int c = ncalls - 1, wi = (nslots & 7) ? ((nslots & 7) >> 1) : 4, any = 0;
   uint8_t code[64];
   for (int s = 0; s < nslots; ++s) { code[s] = 0; any |= err[s]; }
@@ -184,21 +183,14 @@ static void depolarize_row(uint8_t* field /* [2][d][d], written for row `row` on
       if (err[s]) code[s] = (uint8_t)((words[s >> 4] >> (2 * (s & 15))) & 3u);
     left = (16 - (nslots & 15)) & 15;
     cur = left ? (words[nwords - 1] >> (2 * (16 - left))) : 0u;
-    int pool = 0;                                 /* next slot whose positional chunk may still be unused */
     for (int s = 0; s < nslots; ++s) {
       if (!err[s] || code[s]) continue;
       uint32_t v;
       do {
-        while (pool < nslots && err[pool]) ++pool;  /* the error-free slots' chunks come first, in slot order */
-        if (pool < nslots) {
-          v = (words[pool >> 4] >> (2 * (pool & 15))) & 3u;
-          ++pool;
-        } else {
-          if (left == 0) { NEXT_WORD(cur); left = 16; }
-          v = cur & 3u;
-          cur >>= 2;
-          --left;
-        }
+        if (left == 0) { NEXT_WORD(cur); left = 16; }
+        v = cur & 3u;
+        cur >>= 2;
+        --left;
       } while (v == 0);
       code[s] = (uint8_t)v;
     }

@@ -17,9 +17,8 @@
 //    * Pauli codes: 2-bit chunks of the bit stream that starts right behind the row's last slot (bit 16*(2d%8) of call
 //      (2d-1)/8; call 2d/8 when 2d%8 == 0) and runs on through the following calls (c & 15).  Chunk 0 is rejected, chunk
 //      v in {1,2,3} is the Pauli code -- exactly uniform.  Slot s first reads chunk s of the stream (positional, so the
-//      whole row is assigned bit-parallel); the error slots whose chunk was 0, in increasing s, then take further chunks
-//      until theirs is non-zero: first the positional chunks of the row's error-free slots (in slot order), then the
-//      stream from chunk index 2d on.
+//      whole row is assigned bit-parallel); the error slots whose chunk was 0, in increasing s, then take the chunks from
+//      index 2d on, one after the other, until theirs is non-zero.
 //  rejection (ToricCode.py:108-117): attempts are repeated until the syndrome is non-trivial.  When
 //    T * 2d^2 < 2^32 (p * #qubits < 1: most draws would hold no error at all) the field is drawn CONDITIONED
 //    on holding at least one error -- same distribution after the rejection, O(1) attempts at any p:
@@ -126,9 +125,7 @@ __device__ __forceinline__ void depolarize_row(int d, int row, uint32_t elo, uin
   // Pauli codes: 2-bit chunks (chunk 0 rejected, chunk v in {1,2,3} = the code) from the words behind the last slot --
   // 2d is even, so the stream starts on a word boundary: word (2d % 8) / 2 of the last call, or the next call when that
   // one is full.  First pass, bit-parallel: slot s reads chunk s (low bit -> plane A, high bit -> plane B); second pass:
-  // the error slots whose chunk was 0 (a quarter of them), in increasing s, take further chunks -- first the positional
-  // chunks of the error-free slots (in slot order: nobody used them), then the stream from chunk 2d on.  (Without the
-  // pool a row of d=7 has 2 chunks left in its word, and a refill is a whole Philox call for one thread of the warp.)
+  // the error slots whose chunk was 0 (a quarter of them), in increasing s, take further chunks from chunk 2d on.
   int c = ncalls - 1;
   int wi = (nslots & 7) ? ((nslots & 7) >> 1) : 4;   // next word of the current call (4 = exhausted)
   auto next_word = [&]() -> uint32_t {
@@ -156,25 +153,18 @@ __device__ __forceinline__ void depolarize_row(int d, int row, uint32_t elo, uin
   M xs = err & (pa ^ pb);                        // 1:X 2:Y 3:Z -> x = code in {1,2}, z = code in {2,3}
   M zs = err & pb;
   M todo = err & ~(pa | pb);
-  M pool = live & ~err;                          // positional chunks nobody used: the error-free slots'
   while (todo) {
     const int s = first_set(todo);
     todo &= todo - 1;
     uint32_t v;
     do {
-      if (pool) {
-        const int t = first_set(pool);
-        pool &= pool - 1;
-        v = (uint32_t)((pa >> t) & 1) | ((uint32_t)((pb >> t) & 1) << 1);
-      } else {
-        if (left == 0) {
-          cur = next_word();
-          left = 16;
-        }
-        v = cur & 3u;
-        cur >>= 2;
-        --left;
+      if (left == 0) {
+        cur = next_word();
+        left = 16;
       }
+      v = cur & 3u;
+      cur >>= 2;
+      --left;
     } while (v == 0u);
     if (v != 3u) xs |= (M)1 << s;
     if (v != 1u) zs |= (M)1 << s;
