@@ -73,7 +73,10 @@ struct PerspCfg {
   static constexpr bool kWide = (2 * D > 32);
   using TabT = typename std::conditional<kWide, unsigned long long, uint32_t>::type;
   static constexpr int kWarps = TC_WRITE_WARPS;
-  static constexpr int kEpb = 256 / (D <= 8 ? 8 : (D <= 16 ? 16 : 32));   // envs per CTA of the count kernels
+#ifndef TC_COUNT_THREADS
+#define TC_COUNT_THREADS 256
+#endif
+  static constexpr int kEpb = TC_COUNT_THREADS / (D <= 8 ? 8 : (D <= 16 ? 16 : 32));   // envs per CTA of the count kernels
   static constexpr int kPMax = 2 * D * D;
   static constexpr int kDD = D * D;
   static constexpr int kFields = (31 + D - 1) / D + 1;          // row fields overlapping one word

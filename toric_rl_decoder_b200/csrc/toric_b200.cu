@@ -239,11 +239,19 @@ __global__ void __launch_bounds__(kThreads) ground_state_kernel(const uint32_t* 
 // ------------------------------------------------------------------------------------------------
 // perspective count + CTA-local exclusive prefix  (first half of K4)
 // ------------------------------------------------------------------------------------------------
+// CTA size of the kernels that produce the CTA-local perspective prefix (actor_step_kernel, persp_count_kernel); the
+// writer's PerspCfg::kEpb follows it.  Every CTA ends in a barrier, and a CTA that holds an auto-reset keeps the others
+// of its SM slot waiting, so smaller CTAs finish more evenly; the scan kernel then has proportionally more sums to add.
+#ifndef TC_COUNT_THREADS
+#define TC_COUNT_THREADS 256
+#endif
+constexpr int kCountThreads = TC_COUNT_THREADS;
+
 template <int G>
 __device__ __forceinline__ void cta_count_prefix(int count, bool valid, int r, int64_t e,
                                                  int32_t* __restrict__ counts, int32_t* __restrict__ local_off,
                                                  int32_t* __restrict__ block_sum) {
-  constexpr int EPB = kThreads / G;
+  constexpr int EPB = kCountThreads / G;
   __shared__ int sc[32];
   const int ge = threadIdx.x / G;
   if (r == 0) sc[ge] = valid ? count : 0;
@@ -268,12 +276,12 @@ __device__ __forceinline__ void cta_count_prefix(int count, bool valid, int r, i
 }
 
 template <int G>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kCountThreads)
 persp_count_kernel(const uint32_t* __restrict__ syn, int32_t* __restrict__ counts, int32_t* __restrict__ local_off,
                    int32_t* __restrict__ block_sum, int d, int64_t n) {
   const uint32_t gmask = group_mask<G>();
   const int r = threadIdx.x & (G - 1);
-  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  int64_t e = ((int64_t)blockIdx.x * kCountThreads + threadIdx.x) / G;
   const bool valid = e < n;
   if (!valid) e = n - 1;
   Rows s;
@@ -346,14 +354,14 @@ scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ 
 #define TC_ACTOR_MIN_CTAS 5   /* 48 registers: 5 CTAs per SM, 2048 CTAs at 65536 envs = 2.8 waves instead of 3.5 */
 #endif
 template <int G>
-__global__ void __launch_bounds__(kThreads, TC_ACTOR_MIN_CTAS) actor_step_kernel(const ActorArgs a) {
+__global__ void __launch_bounds__(kCountThreads, TC_ACTOR_MIN_CTAS * (256 / kCountThreads)) actor_step_kernel(const ActorArgs a) {
   __shared__ unsigned int s_ctr[kNumCounters];
   if (threadIdx.x < kNumCounters) s_ctr[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t gmask = group_mask<G>();
   const int d = a.d;
   const int r = threadIdx.x & (G - 1);
-  int64_t e = ((int64_t)blockIdx.x * kThreads + threadIdx.x) / G;
+  int64_t e = ((int64_t)blockIdx.x * kCountThreads + threadIdx.x) / G;
   const bool valid = e < a.n;
   if (!valid) e = a.n - 1;
   const bool lead = valid && r == 0;
@@ -495,7 +503,7 @@ struct Workspace {
 
 inline Workspace carve(void* ws, int d, int64_t n) {
   Workspace w;
-  w.epb = kThreads / group_size_for(d);
+  w.epb = kCountThreads / group_size_for(d);
   w.nblocks = (n + w.epb - 1) / w.epb;
   size_t o = 0;
   char* base = static_cast<char*>(ws);
@@ -656,7 +664,7 @@ int actor_pre_impl(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t*
   a.p_thresh = p_thresh; a.counters = counters; a.counts = counts; a.local_off = w.local_off;
   a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
   a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d; a.state_rows = state_rows;
-  TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kThreads, 0, st, a)));
+  TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kCountThreads, 0, st, a)));
   launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, offsets + n,
              counters);
   return launch_status();
@@ -800,7 +808,7 @@ int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void*
   if (!syn || !counts || !workspace) return -1;
   const Workspace w = carve(workspace, d, n);
   if (workspace_bytes < w.bytes) return -2;
-  TC_DISPATCH_G(d, (persp_count_kernel<G><<<(unsigned)w.nblocks, kThreads, 0, st>>>(syn, counts, w.local_off,
+  TC_DISPATCH_G(d, (persp_count_kernel<G><<<(unsigned)w.nblocks, kCountThreads, 0, st>>>(syn, counts, w.local_off,
                                                                                     w.block_sum, d, n)));
   scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, nullptr);
   return launch_status();
