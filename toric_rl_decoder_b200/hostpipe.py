@@ -9,17 +9,20 @@ that contract on the GPU engine and overlaps the PCIe copies with the kernels:
     d2h stream:                    | unpack(k) | results(k)                        | unpack(k+1) | results(k+1)
 
 (two copy streams: on a single one the upload of step k+1 would queue behind the download of step k, which
-waits for compute k, and nothing would overlap)
+waits for compute k, and nothing would overlap; both have a HIGHER PRIORITY than the compute stream -- otherwise the
+download's kernel work queues behind the writer's CTAs and the results leave the GPU only when the writer is done)
 
 Per slot (ring of `depth`): a device action buffer, one contiguous device staging block
-[reward f32 | counts i32 | terminal u8 | states u8 (n,2,d,d)] and its pinned host twin, so every step moves
-exactly one H2D and one D2H memcpy.  The perspective tensor stays on the device, where the reference also
-puts it (`.to(device)`, src/numba/util_actor.py:39).
+[reward f32 | counts i32 | terminal u8 | states] and its pinned host twin, so every step moves exactly one H2D and
+one D2H memcpy; the whole step is enqueued by one native call (tc_host_actor_step).  `states` is the row-packed form
+by default (written by the step kernel itself, seen on the host through a LazyStates view) or the reference's
+one-byte-per-stabiliser array.  The perspective tensor stays on the device, where the reference also puts it
+(`.to(device)`, src/numba/util_actor.py:39).  depth=1 is the closed loop of EnvSet.step's contract.
 """
+import ctypes
+
 import numpy as np
 import torch
-
-import ctypes
 
 from . import _lib
 from .engine import ACTOR_AUTO_RESET, _Range
