@@ -264,7 +264,7 @@ def _torch_reference_perspectives(state, pos, env_of, d):
 
 
 @pytest.mark.parametrize("d,n", ((7, 65536), (5, 30000), (8, 4096), (4, 8192), (3, 5000), (3, 300001), (9, 8192), (15, 4096),
-                                 (25, 1024), (32, 300)))
+                                 (25, 1024), (32, 300), (4, 530001)))      # the last two d <= 4 sizes: multi-CTA scan
 def test_full_size_properties(pkg, d, n):
     """BASELINE configs[1] size (d=7, 65536 envs) and the other lattice sizes / both writer code paths: after a
     few fused steps, every perspective equals an independent torch gather; counts equal the popcount of the

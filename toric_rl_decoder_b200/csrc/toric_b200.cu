@@ -292,20 +292,60 @@ persp_count_kernel(const uint32_t* __restrict__ syn, int32_t* __restrict__ count
   cta_count_prefix<G>(count, valid, r, e, counts, local_off, block_sum);
 }
 
-// single CTA: exclusive scan of the per-CTA sums -> block_off (int64), grand total -> offsets[n].
-// Warp w owns a contiguous chunk of ceil(nblocks/32) sums and walks it in 32-wide tiles (coalesced 128-byte
-// reads, no CTA barrier inside the loops): pass 1 adds the chunk up, the 32 chunk totals are scanned once,
-// pass 2 re-reads the chunk and writes the running prefix.
+// Exclusive scan of the per-CTA sums -> block_off (int64), grand total -> offsets[n].
+// One CTA handles up to kScanChunk sums: warp w owns a contiguous piece of them and walks it in 32-wide tiles (coalesced
+// 128-byte reads, no CTA barrier inside the loops): pass 1 adds the piece up, the 32 piece totals are scanned once,
+// pass 2 re-reads the piece and writes the running prefix.  Batches with more than kScanChunk count-CTAs (2^18 envs at
+// d <= 8) first reduce every chunk (scan_chunk_sums_kernel) and then run one scan CTA per chunk, each starting from the
+// sum of the chunks in front of it -- a single CTA walking 131 072 sums was 0.25 ms at 2^22 envs.
+constexpr int kScanChunk = 8192;
+
 __global__ void __launch_bounds__(1024)
-scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ block_off, int64_t nblocks,
-                   int64_t* __restrict__ total_out, int64_t* __restrict__ counters) {
+scan_chunk_sums_kernel(const int32_t* __restrict__ block_sum, int64_t nblocks, long long* __restrict__ chunk_sum) {
   __shared__ long long warp_tot[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  pdl_wait();                 // block_sum comes from the kernel in front
+  pdl_wait();
   pdl_launch_dependents();
-  const int64_t chunk = ((nblocks + 1023) / 1024) * 32;          // multiple of the tile width
-  const int64_t lo = (int64_t)warp * chunk < nblocks ? (int64_t)warp * chunk : nblocks;
-  const int64_t hi = lo + chunk < nblocks ? lo + chunk : nblocks;
+  const int64_t c0 = (int64_t)blockIdx.x * kScanChunk;
+  const int64_t c1 = c0 + kScanChunk < nblocks ? c0 + kScanChunk : nblocks;
+  long long sum = 0;
+  for (int64_t i = c0 + tid; i < c1; i += 1024) sum += (long long)block_sum[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) warp_tot[warp] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    sum = warp_tot[lane];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) chunk_sum[blockIdx.x] = sum;
+  }
+}
+
+__global__ void __launch_bounds__(1024)
+scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ block_off, int64_t nblocks,
+                   int64_t* __restrict__ total_out, int64_t* __restrict__ counters,
+                   const long long* __restrict__ chunk_sum) {
+  __shared__ long long warp_tot[32];
+  __shared__ long long s_base;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_wait();                 // block_sum (and chunk_sum) come from the kernels in front
+  pdl_launch_dependents();
+  // this CTA's sums [c0, c1); with a single CTA that is everything (chunk_sum == nullptr)
+  const int64_t c0 = chunk_sum ? (int64_t)blockIdx.x * kScanChunk : 0;
+  const int64_t c1 = chunk_sum ? (c0 + kScanChunk < nblocks ? c0 + kScanChunk : nblocks) : nblocks;
+  if (warp == 0) {            // sum of the chunks in front (at most a few dozen)
+    long long b = 0;
+    if (chunk_sum)
+      for (int c = lane; c < (int)blockIdx.x; c += 32) b += chunk_sum[c];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) b += __shfl_xor_sync(0xffffffffu, b, o);
+    if (lane == 0) s_base = b;
+  }
+  const int64_t len = c1 - c0;
+  const int64_t piece = ((len + 1023) / 1024) * 32;              // multiple of the tile width
+  const int64_t lo = c0 + ((int64_t)warp * piece < len ? (int64_t)warp * piece : len);
+  const int64_t hi = lo + piece < c1 ? lo + piece : c1;
   long long sum = 0;
 #pragma unroll 4
   for (int64_t i = lo + lane; i < hi; i += 32) sum += (long long)block_sum[i];
@@ -313,6 +353,7 @@ scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ 
   for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
   if (lane == 0) warp_tot[warp] = sum;
   __syncthreads();
+  const long long base = s_base;
   if (warp == 0) {
     const long long w = warp_tot[lane];
     long long winc = w;
@@ -321,17 +362,17 @@ scan_blocks_kernel(const int32_t* __restrict__ block_sum, int64_t* __restrict__ 
       const long long t = __shfl_up_sync(0xffffffffu, winc, o);
       if (lane >= o) winc += t;
     }
-    warp_tot[lane] = winc - w;   // exclusive prefix of the chunk totals
-    if (lane == 31) {
-      *total_out = winc;
+    warp_tot[lane] = winc - w;   // exclusive prefix of the piece totals
+    if (lane == 31 && c1 == nblocks) {          // the CTA that holds the last sums knows the grand total
+      *total_out = base + winc;
       if (counters) atomicAdd(reinterpret_cast<unsigned long long*>(counters + kCtrPerspectives),
-                              (unsigned long long)winc);
+                              (unsigned long long)(base + winc));
     }
   }
   __syncthreads();
-  long long carry = warp_tot[warp];
-  for (int64_t base = lo; base < hi; base += 32) {
-    const int64_t i = base + lane;
+  long long carry = base + warp_tot[warp];
+  for (int64_t t0 = lo; t0 < hi; t0 += 32) {
+    const int64_t i = t0 + lane;
     const int v = i < hi ? block_sum[i] : 0;
     int inc = v;                 // a tile of 32 CTA sums stays far below 2^31 (<= 32 * 32 * 2 * 32 * 32)
 #pragma unroll
@@ -498,6 +539,8 @@ struct Workspace {
   int64_t nblocks;
   int epb;
   ScanWs scan;        // single-pass step: launch counter + look-back descriptors (never touched by the other kernels)
+  long long* chunk_sum;   // [ceil(nblocks / kScanChunk)]: multi-CTA scan of large batches
+  int64_t nchunks;
   size_t bytes;
 };
 
@@ -521,8 +564,34 @@ inline Workspace carve(void* ws, int d, int64_t n) {
   o += (size_t)((n + 31) / 32) * 8;
   w.scan.desc0 = reinterpret_cast<uint32_t*>(base + o);
   o += (size_t)n * 4;
+  o = (o + 15) & ~(size_t)15;
+  w.nchunks = (w.nblocks + kScanChunk - 1) / kScanChunk;
+  w.chunk_sum = reinterpret_cast<long long*>(base + o);
+  o += (size_t)w.nchunks * 8;
   w.bytes = (o + 255) & ~(size_t)255;
   return w;
+}
+
+// cross-CTA scan of the perspective counts: one CTA up to kScanChunk count-CTAs, else chunk sums + one CTA per chunk
+inline void launch_scan(const Workspace& w, int64_t* total_out, int64_t* counters, cudaStream_t st, bool pdl) {
+  if (w.nblocks <= kScanChunk) {
+    if (pdl)
+      launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, total_out,
+                 counters, (const long long*)nullptr);
+    else
+      scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, total_out, counters, nullptr);
+    return;
+  }
+  if (pdl) {
+    launch_pdl(scan_chunk_sums_kernel, (unsigned)w.nchunks, 1024, 0, st, (const int32_t*)w.block_sum, w.nblocks,
+               w.chunk_sum);
+    launch_pdl(scan_blocks_kernel, (unsigned)w.nchunks, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off,
+               w.nblocks, total_out, counters, (const long long*)w.chunk_sum);
+  } else {
+    scan_chunk_sums_kernel<<<(unsigned)w.nchunks, 1024, 0, st>>>(w.block_sum, w.nblocks, w.chunk_sum);
+    scan_blocks_kernel<<<(unsigned)w.nchunks, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, total_out, counters,
+                                                            w.chunk_sum);
+  }
 }
 
 // persistent grid: one CTA slot per (SM x resident CTAs), capped by the number of envs
@@ -665,8 +734,7 @@ int actor_pre_impl(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t*
   a.block_sum = w.block_sum; a.key = make_key(seed); a.env_base = env_base; a.n = n; a.flags = flags;
   a.max_steps = max_steps; a.mode = mode; a.n_fixed = n_fixed; a.d = d; a.state_rows = state_rows;
   TC_DISPATCH_G(d, (launch_pdl(actor_step_kernel<G>, (unsigned)w.nblocks, kCountThreads, 0, st, a)));
-  launch_pdl(scan_blocks_kernel, 1, 1024, 0, st, (const int32_t*)w.block_sum, w.block_off, w.nblocks, offsets + n,
-             counters);
+  launch_scan(w, offsets + n, counters, st, true);
   return launch_status();
 }
 
@@ -810,7 +878,7 @@ int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void*
   if (workspace_bytes < w.bytes) return -2;
   TC_DISPATCH_G(d, (persp_count_kernel<G><<<(unsigned)w.nblocks, kCountThreads, 0, st>>>(syn, counts, w.local_off,
                                                                                     w.block_sum, d, n)));
-  scan_blocks_kernel<<<1, 1024, 0, st>>>(w.block_sum, w.block_off, w.nblocks, offsets + n, nullptr);
+  launch_scan(w, offsets + n, nullptr, st, false);
   return launch_status();
 }
 
