@@ -110,10 +110,30 @@ struct PerspCfg {
   static constexpr int kSmemBytes = kCandBytes + kWarps * kWarpBytes;
 };
 
+// TC_TMA_L2_HINT: 0 = none (default), 1 = evict_first, 2 = evict_last, 3 = no_allocate-like evict_first at fraction 0
+// -- an L2 eviction-priority hint on the bulk stores (the output is never re-read by this kernel); A/B in
+// profiles/r02_ab_tma_l2_hint.txt
+#ifndef TC_TMA_L2_HINT
+#define TC_TMA_L2_HINT 0
+#endif
 __device__ __forceinline__ void bulk_store(void* gdst, const void* ssrc, int bytes) {
   const uint32_t sa = (uint32_t)__cvta_generic_to_shared(ssrc);
+#if TC_TMA_L2_HINT == 0
   asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(sa), "r"(bytes)
                : "memory");
+#else
+  unsigned long long pol;
+#if TC_TMA_L2_HINT == 1
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+#elif TC_TMA_L2_HINT == 2
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+#else
+  asm volatile("createpolicy.fractional.L2::evict_unchanged.b64 %0, 1.0;" : "=l"(pol));
+#endif
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(sa),
+               "r"(bytes), "l"(pol)
+               : "memory");
+#endif
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
 
