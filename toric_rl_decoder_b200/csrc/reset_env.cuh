@@ -116,4 +116,99 @@ reset_env_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint
   }
 }
 
+// The same idea for 9 <= d <= 16 (a row pair still fits a 32-bit slot mask, a plane no longer fits a register pair): the
+// thread keeps its env's 6d row words in shared memory, word-major with a padded pitch -- S(w, t) = smem[w * (T + 1) + t] --
+// so that both the thread-major accesses while sampling (consecutive t) and the env-major copy-out (consecutive w of one
+// env: bank (w + env) % 32) are free of bank conflicts.
+constexpr int kResetRowsThreads = 128;
+constexpr int kResetRowsPitch = kResetRowsThreads + 1;
+
+template <int D>
+constexpr int reset_rows_smem_bytes() { return 6 * D * kResetRowsPitch * 4; }
+
+template <int D>
+__global__ void __launch_bounds__(kResetRowsThreads)
+reset_rows_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint8_t* __restrict__ gs,
+                  uint8_t* __restrict__ status, const uint32_t* __restrict__ p_thresh, uint32_t* __restrict__ episode,
+                  const int64_t* __restrict__ idx, int64_t n_idx, int one_draw, uint2 key, int64_t env_base) {
+  static_assert(D > 8 && D <= 16, "row pairs must fit a 32-bit slot mask");
+  constexpr int nq = 2 * D * D;
+  extern __shared__ uint32_t rows_smem[];
+  const int t = threadIdx.x;
+  uint32_t* S = rows_smem + t;                   // S[w * pitch]: word w of this thread's env
+  constexpr int P = kResetRowsPitch;
+  const int64_t k0 = (int64_t)blockIdx.x * kResetRowsThreads;
+  const int64_t k = k0 + t;
+  const bool valid = k < n_idx;
+  const int64_t e = valid ? (idx ? idx[k] : k) : 0;
+  uint32_t ep = 0;
+  uint8_t st = 0;
+  if (valid) {
+    ep = episode[e];
+    const uint32_t thresh = p_thresh[e];
+    const uint64_t env_id = (uint64_t)(env_base + e);
+    const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
+    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
+    if (conditioned && thresh == 0u) {
+      st = kStatusResetGaveUp;
+#pragma unroll 1
+      for (int w = 0; w < 6 * D; ++w) S[w * P] = 0u;
+    } else {
+      uint32_t attempt = 0;
+      while (true) {
+        int first_q = -1;
+        if (conditioned) {
+          const uint4 rf = philox4x32_10(make_uint4(elo, ehi, ep, kDomFirst | attempt), key);
+          first_q = first_error_index(thresh, nq, rf.x, rf.y);
+        }
+#pragma unroll 1
+        for (int row = 0; row < D; ++row) {
+          uint32_t rx0, rz0, rx1, rz1;
+          depolarize_row<uint32_t>(D, row, elo, ehi, ep, attempt, thresh, key, first_q, rx0, rz0, rx1, rz1);
+          S[(0 * D + row) * P] = rx0;
+          S[(1 * D + row) * P] = rx1;
+          S[(2 * D + row) * P] = rz0;
+          S[(3 * D + row) * P] = rz1;
+        }
+        uint32_t any = 0;
+#pragma unroll 1
+        for (int r = 0; r < D; ++r) {            // createSyndromOpt (ToricCode.py:168-199), row by row
+          const int up = r == 0 ? D - 1 : r - 1, dn = r + 1 == D ? 0 : r + 1;
+          const uint32_t z1r = S[(3 * D + r) * P], x0r = S[(0 * D + r) * P];
+          const uint32_t v = S[(2 * D + r) * P] ^ S[(2 * D + up) * P] ^ z1r ^ rotl_d(z1r, D);
+          const uint32_t pl = x0r ^ rotr_d(x0r, D) ^ S[(1 * D + r) * P] ^ S[(1 * D + dn) * P];
+          S[(4 * D + r) * P] = v;
+          S[(5 * D + r) * P] = pl;
+          any |= v | pl;
+        }
+        ++attempt;
+        if (any != 0u || one_draw) break;
+        if (attempt >= kMaxAttempts) { st = kStatusResetGaveUp; break; }
+      }
+    }
+  }
+  __syncthreads();
+  if (idx == nullptr) {                          // the CTA's envs are consecutive: coalesced copies, env-major in HBM
+    const int64_t rest = n_idx - k0;
+    const int cnt = rest < kResetRowsThreads ? (int)rest : kResetRowsThreads;
+    uint32_t* gq = qubits + k0 * 4 * D;
+    for (int g = t; g < cnt * 4 * D; g += kResetRowsThreads) gq[g] = rows_smem[(g % (4 * D)) * P + g / (4 * D)];
+    uint32_t* gsyn = syn + k0 * 2 * D;
+    for (int g = t; g < cnt * 2 * D; g += kResetRowsThreads)
+      gsyn[g] = rows_smem[(4 * D + g % (2 * D)) * P + g / (2 * D)];
+  } else if (valid) {                            // listed envs: scattered, written per thread
+    uint32_t* gq = qubits + e * 4 * D;
+    uint32_t* gsyn = syn + e * 2 * D;
+#pragma unroll 1
+    for (int w = 0; w < 4 * D; ++w) gq[w] = S[w * P];
+#pragma unroll 1
+    for (int w = 0; w < 2 * D; ++w) gsyn[w] = S[(4 * D + w) * P];
+  }
+  if (valid) {
+    episode[e] = ep + 1;
+    if (gs) gs[e] = 1;
+    if (status && st) status[e] |= st;
+  }
+}
+
 }  // namespace tc

@@ -838,6 +838,29 @@ int tc_reset(uint32_t* qubits, uint32_t* syn, uint8_t* gs, uint8_t* status, cons
     }
     return launch_status();
   }
+  if (base_mode == 0 && d <= 16) {    // 9..16: one thread per env, rows in shared memory (csrc/reset_env.cuh)
+    const int one_draw = (mode & TC_SAMPLE_ONE_DRAW) ? 1 : 0;
+    const unsigned grid = grid_for(n_idx, kResetRowsThreads);
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    switch (d) {
+#define TC_CASE(D)                                                                                                      \
+  case D: {                                                                                                             \
+    static std::once_flag once[64];                                                                                     \
+    std::call_once(once[dev], [] {                                                                                      \
+      cudaFuncSetAttribute(reset_rows_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize,                           \
+                           reset_rows_smem_bytes<D>());                                                                 \
+    });                                                                                                                 \
+    reset_rows_kernel<D><<<grid, kResetRowsThreads, reset_rows_smem_bytes<D>(), st>>>(                                  \
+        qubits, syn, gs, status, p_thresh, episode, idx, n_idx, one_draw, make_key(seed), env_base);                    \
+  } break;
+      TC_CASE(9) TC_CASE(10) TC_CASE(11) TC_CASE(12) TC_CASE(13) TC_CASE(14) TC_CASE(15) TC_CASE(16)
+#undef TC_CASE
+    }
+    return launch_status();
+  }
 #endif
   switch (d) {
 #define TC_CASE(D)                                                                                              \
