@@ -14,14 +14,14 @@ def _thresh(p):
 
 
 @pytest.mark.parametrize("d,p,n", ((7, 0.1, 60000), (7, 0.005, 200000), (7, 0.0005, 200000), (5, 0.0005, 200000),
-                                   (9, 0.02, 60000), (7, 0.0101, 150000), (7, 0.0103, 150000), (25, 0.05, 600)))
+                                   (9, 0.02, 60000), (7, 0.0812, 100000), (7, 0.0820, 100000), (25, 0.05, 600)))
 def test_depolarizing_law(d, p, n):
-    """p = 0.0101 / 0.0103 straddle p * 2d^2 = 1 at d=7: the conditioned sampler below, the plain rejection loop
+    """p = 0.0812 / 0.0820 straddle p * 2d^2 = 8 at d=7: the conditioned sampler below, the plain rejection loop
     above -- both must give the same law."""
     q, s, att = C.reset_batch(d, n, 1 << 33, 2, _thresh(p), 99)
     assert (s.reshape(n, -1).sum(1) > 0).all() and (att < (1 << 20)).all()
     nq = 2 * d * d
-    if _thresh(p) * nq < (1 << 32):
+    if _thresh(p) * nq < (8 << 32):
         assert att.mean() < 1.001                     # conditioned on >= 1 error: (almost) never rejected
     S.check_depolarizing(q, p)
     if n >= 20000:

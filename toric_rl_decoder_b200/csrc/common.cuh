@@ -71,6 +71,10 @@ constexpr uint32_t kDomAction = 0xC0000000u;   // random-policy action draws
 constexpr uint32_t kMaxAttempts = 1u << 20;    // depolarizing rejection attempts
 constexpr uint32_t kMaxFixedAttempts = 1u << 10;
 constexpr int kSampleOneDraw = 16;             // TC_SAMPLE_ONE_DRAW (OR-ed into the sampling mode)
+// The depolarizing reset draws its field conditioned on >= 1 error while p * #qubits < kCondMeanErrors (sampler.cuh).
+// At 8 an unconditioned draw is empty with probability < e^-8 = 3e-4, so a rejection pass -- which in the
+// one-thread-per-env kernels stalls the whole warp -- is rare on both sides of the switch.
+constexpr unsigned long long kCondMeanErrors = 8;
 
 // ---------------------------------------------------------------------------------------------
 // Programmatic dependent launch: the three kernels of one actor step (and the first kernel of the next

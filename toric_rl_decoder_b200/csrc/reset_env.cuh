@@ -45,7 +45,7 @@ reset_env_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uint
     const uint32_t thresh = p_thresh[e];
     const uint64_t env_id = (uint64_t)(env_base + e);
     const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
-    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
+    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (kCondMeanErrors << 32);
     if (conditioned && thresh == 0u) {
       st = kStatusResetGaveUp;                   // p == 0: nothing to condition on (sampler.cuh)
     } else {
@@ -148,7 +148,7 @@ reset_rows_kernel(uint32_t* __restrict__ qubits, uint32_t* __restrict__ syn, uin
     const uint32_t thresh = p_thresh[e];
     const uint64_t env_id = (uint64_t)(env_base + e);
     const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
-    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
+    const bool conditioned = !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (kCondMeanErrors << 32);
     if (conditioned && thresh == 0u) {
       st = kStatusResetGaveUp;
 #pragma unroll 1

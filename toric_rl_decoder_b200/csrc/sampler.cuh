@@ -20,7 +20,7 @@
 //      whole row is assigned bit-parallel); the error slots whose chunk was 0, in increasing s, then take the chunks from
 //      index 2d on, one after the other, until theirs is non-zero.
 //  rejection (ToricCode.py:108-117): attempts are repeated until the syndrome is non-trivial.  When
-//    T * 2d^2 < 2^32 (p * #qubits < 1: most draws would hold no error at all) the field is drawn CONDITIONED
+//    T * 2d^2 < 8 * 2^32 (p * #qubits < 8: an empty draw is not yet negligible, e^-8) the field is drawn CONDITIONED
 //    on holding at least one error -- same distribution after the rejection, O(1) attempts at any p:
 //    word3 = 0x40000000 | attempt gives U = ((w0<<32 | w1) >> 11) * 2^-53; the first error sits at linear index
 //    K = min(2d^2-1, floor(log1p(-U*A) / log1p(-p))), A = 1 - (1-p)^(2d^2), in the order q = m*d*d + i*d + j
@@ -188,7 +188,7 @@ __device__ __forceinline__ void sample_errors(uint32_t gmask, int d, int r, uint
   const uint32_t pm = 0xffffffffu >> __clz(nq - 1);      // smallest 2^k - 1 >= nq - 1 (nq >= 18)
   const uint32_t elo = (uint32_t)env_id, ehi = (uint32_t)(env_id >> 32);
   const uint32_t cap = (mode == 0) ? kMaxAttempts : kMaxFixedAttempts;
-  const bool conditioned = mode == 0 && !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (1ull << 32);
+  const bool conditioned = mode == 0 && !one_draw && (unsigned long long)thresh * (unsigned long long)nq < (kCondMeanErrors << 32);
   uint32_t attempt = 0;
   if (conditioned && thresh == 0u) {             // p == 0: nothing to condition on
     s.x0 = s.x1 = s.z0 = s.z1 = 0;
