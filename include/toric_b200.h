@@ -111,6 +111,38 @@ int tc_perspectives(const uint32_t* syn, float* out, uint8_t* pos, int32_t* coun
                     int32_t* overflow, int64_t cap, void* workspace, size_t workspace_bytes, int d,
                     int64_t n, void* stream);
 
+/* tc_perspectives without the workspace argument -- NO COUNTERPART IN THE REFERENCE (which is Python and allocates
+ * freely); it exists for the caller's sake.  Same kernels, same outputs bit for bit.
+ *
+ * Who needs it: code that hands this library device buffers it was itself given and that has no way to get more
+ * device memory at the point of the call -- an operator inside a host framework whose memory pool it may not touch
+ * (cudaMalloc from there bypasses the pool, and cudaFree synchronises the whole device), a process that gave all
+ * device memory to one arena at start-up so that the driver has nothing left to hand out, or a real-time decoding
+ * loop that must not wait on the allocator's lock.  Such a caller still owns its inputs and
+ * outputs (syn, out, pos, counts, offsets, overflow) but cannot produce the tc_workspace_bytes(d, n) scratch
+ * block, so the scratch comes from an array compiled into the library instead.
+ *
+ * The price and the limit: the array is TC_STATIC_SCRATCH_BYTES (1 MiB) of device memory on EVERY GPU that loads
+ * the library, held until the process exits even if this entry point is never called.  A batch is accepted when
+ * tc_workspace_bytes(d, n) <= TC_STATIC_SCRATCH_BYTES -- at least TC_STATIC_MAX_ENVS (65 536) envs for every d;
+ * anything larger returns -2 and prints one line to stderr saying how many bytes were needed (split the batch, or
+ * use tc_perspectives).  The library calls no cudaMalloc / cudaFree / allocating routine on this path.
+ *
+ * First call on a device: the library looks up that device's address of the array (cudaGetSymbolAddress, with the
+ * device of the call current) and sets the writer kernel's shared-memory attribute.  Make that first call per
+ * device during start-up, before any stream capture begins.  Later calls only enqueue kernels.  The array used is
+ * the CURRENT device's: syn and the outputs must live there, as for every other entry point.
+ *
+ * Sharing: there is ONE array per device for all callers, streams and threads of the process, and it keeps
+ * whatever the last call left in it.  That is harmless from call to call (every word this path reads is rewritten
+ * by the same call first, nothing needs clearing), but two calls whose kernels can run at the same time on one GPU
+ * -- different streams, or different host threads -- overwrite each other's prefix sums and produce garbage without
+ * any error.  Serialise them: one stream, or an event between the calls. */
+#define TC_STATIC_SCRATCH_BYTES (1u << 20)
+#define TC_STATIC_MAX_ENVS 65536
+int tc_perspectives_static(const uint32_t* syn, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
+                           int32_t* overflow, int64_t cap, int d, int64_t n, void* stream);
+
 /* The two halves of tc_perspectives, for callers that time or overlap them separately:
  * count + scan (fills counts, offsets[n] and the workspace), then the streaming write. */
 int tc_persp_count(const uint32_t* syn, int32_t* counts, int64_t* offsets, void* workspace,

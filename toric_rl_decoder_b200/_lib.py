@@ -39,6 +39,7 @@ SIGNATURES = {
     "tc_reset": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _u64, _i64, _i, _vp],
     "tc_ground_state": [_vp, _vp, _i, _i64, _vp],
     "tc_perspectives": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
+    "tc_perspectives_static": [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i64, _vp],
     "tc_persp_count": [_vp, _vp, _vp, _vp, _sz, _i, _i64, _vp],
     "tc_persp_write": [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
     "tc_persp_write_as": [_vp, _vp, _i, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],

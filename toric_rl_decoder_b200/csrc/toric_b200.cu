@@ -2,6 +2,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
 #include "../../include/toric_b200.h"
 
+#include <cstdio>
 #include <mutex>
 
 #include "common.cuh"
@@ -738,6 +739,37 @@ int actor_pre_impl(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t*
   return launch_status();
 }
 
+// ---- built-in scratch of tc_perspectives_static -----------------------------------------------------------------
+// Lives in the library image: every GPU that loads libtoric_b200.so holds TC_STATIC_SCRATCH_BYTES of it until the
+// process exits, whether or not the entry point is ever called.  One array per device, shared by all callers.
+static __device__ __align__(256) unsigned char g_static_scratch[TC_STATIC_SCRATCH_BYTES];
+
+// Device address of the CURRENT device's copy of g_static_scratch.  On the host the name `g_static_scratch` is only
+// a handle for the runtime's symbol table -- handing it to a kernel would pass a host address -- so the real address
+// is asked for once per device (with that device current) and remembered.  A failed lookup is not remembered: the
+// next call tries again.  Devices past the table are looked up on every call.
+int static_scratch(void** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static void* addr[kMaxDev] = {nullptr};
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) return (int)err;
+  const bool cached = dev >= 0 && dev < kMaxDev;
+  std::lock_guard<std::mutex> lock(mu);
+  if (cached && addr[dev]) {
+    *out = addr[dev];
+    return 0;
+  }
+  void* p = nullptr;
+  err = cudaGetSymbolAddress(&p, g_static_scratch);
+  if (err != cudaSuccess) return (int)err;
+  if (!p) return (int)cudaErrorInvalidSymbol;
+  if (cached) addr[dev] = p;
+  *out = p;
+  return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -951,6 +983,31 @@ int tc_perspectives(const uint32_t* syn, float* out, uint8_t* pos, int32_t* coun
   const int rc = tc_persp_count(syn, counts, offsets, workspace, workspace_bytes, d, n, stream);
   if (rc != 0) return rc;
   return tc_persp_write(syn, out, pos, offsets, overflow, cap, workspace, workspace_bytes, d, n, stream);
+}
+
+// tc_perspectives for callers that have no device allocator to take a workspace from (see the header).  The count,
+// scan and writer kernels are the ones tc_perspectives launches; only the workspace differs: it is the current
+// device's g_static_scratch.  Nothing in it has to be cleared between calls -- local_off, block_sum, block_off and
+// chunk_sum are each rewritten in full for (d, n) by the count / scan kernels of this call before the writer reads
+// them, and the look-back descriptors of the single-pass step (the one region that must start at zero) are not used
+// on this path.  No cudaMalloc / cudaFree here or below: the set-up is cudaGetSymbolAddress, and the writer's
+// once-per-device cudaFuncSetAttribute / occupancy query.
+int tc_perspectives_static(const uint32_t* syn, float* out, uint8_t* pos, int32_t* counts, int64_t* offsets,
+                           int32_t* overflow, int64_t cap, int d, int64_t n, void* stream) {
+  if (bad_d(d) || n < 0) return -1;
+  const size_t need = carve(nullptr, d, n).bytes;
+  if (need > (size_t)TC_STATIC_SCRATCH_BYTES) {
+    fprintf(stderr,
+            "tc_perspectives_static: %lld envs of size %d need %zu bytes of scratch, the built-in array holds %zu "
+            "(TC_STATIC_SCRATCH_BYTES); split the batch or use tc_perspectives with a caller-owned workspace\n",
+            (long long)n, d, need, (size_t)TC_STATIC_SCRATCH_BYTES);
+    return -2;
+  }
+  void* scratch = nullptr;
+  const int rc = static_scratch(&scratch);
+  if (rc != 0) return rc;
+  return tc_perspectives(syn, out, pos, counts, offsets, overflow, cap, scratch, (size_t)TC_STATIC_SCRATCH_BYTES, d, n,
+                         stream);
 }
 
 int tc_actor_pre(uint32_t* qubits, uint32_t* syn, uint32_t* prev_syn, int32_t* actions, float* reward,
