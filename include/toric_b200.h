@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define TC_ABI_VERSION 5
+#define TC_ABI_VERSION 6
 #define TC_NUM_COUNTERS 16
 
 /* status bits written per env */
@@ -233,7 +233,7 @@ int tc_host_actor_step(const tc_host_step* s);
  *   sel_idx   int64   [n]         out: global row of the chosen perspective, -1 when the env has none (nullable)
  *   was_greedy uint8  [n]         out: 1 greedy / 0 random (nullable)
  * Greedy = first maximum in row-major (perspective, action) order (np.argmax tie-break).  The decision is
- * drawn on device: Philox(seed; env_base+e, episode[e], 0x40000000|steps[e]) -> random iff u0 < eps
+ * drawn on device: Philox(seed; env_base+e, episode[e], 0x60000000|(steps[e] & 0x1fffffff)) -> random iff u0 < eps
  * threshold (eps_thresh uint32 [n] per env, or eps_scalar when NULL; threshold = floor(eps * 2^32)),
  * random perspective mulhi(u1, P), random action mulhi(u2, 3); greedy_in (uint8 [n], nullable) overrides
  * the decision.  episode / steps nullable (0).  Envs without perspectives get the identity action

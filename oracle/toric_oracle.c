@@ -218,7 +218,7 @@ uint32_t to_reset(uint8_t* q, uint8_t* s, int d, uint64_t env_id, uint32_t episo
   uint32_t pm = 1;
   while ((int)pm < nq) pm <<= 1;
   pm -= 1;
-  const uint32_t cap = mode == 0 ? (1u << 20) : (1u << 10);
+  const uint32_t cap = mode == 0 ? (1u << 20) : (1u << 9);   /* 9 attempt bits in the fixed-weight counter (common.cuh) */
   const int conditioned = mode == 0 && !one_draw && (uint64_t)thresh * (uint64_t)nq < (8ull << 32);
   uint32_t attempt = 0, rnd[4];
   uint8_t field[2 * 32 * 32];

@@ -26,7 +26,7 @@ def test_header_symbols_exported(lib_path):
     assert len(names) >= 14
     for n in names:
         assert hasattr(lib, n), "missing export %s" % n
-    assert lib.tc_abi_version() == 5
+    assert lib.tc_abi_version() == 6
 
 
 def test_binding_covers_header(lib_path):

@@ -73,7 +73,7 @@ def test_select_action_epsilon_draws(pkg, d, n, eps):
     rp, ra = np.zeros(n, np.int64), np.zeros(n, np.int64)
     for e in range(n):
         g = base + e
-        u = C.philox((g & 0xffffffff, g >> 32, int(ep[e]) & 0xffffffff, 0x40000000 | int(st[e])), (seed & 0xffffffff, seed >> 32))
+        u = C.philox((g & 0xffffffff, g >> 32, int(ep[e]) & 0xffffffff, 0x60000000 | int(st[e])), (seed & 0xffffffff, seed >> 32))
         greedy[e] = not (int(u[0]) < th)
         rp[e] = (int(u[1]) * int(cn[e])) >> 32
         ra[e] = (int(u[2]) * 3) >> 32
@@ -84,6 +84,34 @@ def test_select_action_epsilon_draws(pkg, d, n, eps):
     k = int((~greedy).sum())
     sigma = max(np.sqrt(n * eps * (1 - eps)), 1e-9)
     assert abs(k - n * eps) <= 5 * sigma + 1e-6
+
+
+def test_select_and_first_error_draws_are_independent(pkg):
+    """The epsilon-greedy draw of (episode E, step 0) and the first-error draw (attempt 0) of the conditioned reset
+    that runs with episode counter E live in different Philox counter domains (csrc/common.cuh).  When they shared
+    0x40000000, "random action" meant U < eps for the reset as well, i.e. a first error at a low linear index: the
+    mean first-error position of the exploring envs then sat far below that of the greedy ones."""
+    d, n, eps, seed, base = 5, 1 << 16, 0.5, 4242, 77
+    eng = pkg.ToricEngine(d, n, seed=seed, env_base=base, p_error=0.05)      # p * 2d^2 = 2.5 < 8: conditioned sampler
+    st = np.zeros((n, 2, d, d), np.uint8)
+    st[:, 0, 1, 1] = 1
+    eng.set_state(st)                                                         # one defect: every env has perspectives
+    eng.perspectives()
+    persp, pos, counts, offsets = eng.perspective_views()
+    q = torch.zeros((persp.shape[0], 3), dtype=torch.float32, device="cuda")
+    was = torch.empty(n, dtype=torch.uint8, device="cuda")
+    pkg.select_action_device(q, pos, offsets, n, epsilon=eps, episode=eng.episode, steps=eng.steps, seed=seed,
+                             env_base=base, was_greedy=was)
+    eng.reset()                                                               # same episode counter as the draw above
+    torch.cuda.synchronize()
+    codes = eng.get_qubits().cpu().numpy().reshape(n, -1)
+    first = (codes != 0).argmax(axis=1).astype(np.float64)                    # q = m*d*d + i*d + j of the first error
+    explore = was.cpu().numpy() == 0
+    k = int(explore.sum())
+    assert abs(k - n * eps) <= 5 * np.sqrt(n * eps * (1 - eps))
+    diff = first[explore].mean() - first[~explore].mean()
+    sigma = first.std() * np.sqrt(1.0 / k + 1.0 / (n - k))
+    assert abs(diff) <= 5 * sigma, (diff, sigma)
 
 
 def test_select_action_empty_segments(pkg):

@@ -55,7 +55,7 @@ SIGNATURES = {
     "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],
 }
 
-ABI_VERSION = 5
+ABI_VERSION = 6
 _lib = None
 
 

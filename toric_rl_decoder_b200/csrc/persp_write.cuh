@@ -108,6 +108,8 @@ struct PerspCfg {
   static constexpr int kStageBufs = D == 3 ? 1 : kStageBufsDefault;
   static constexpr int kWarpBytes = kStageBufs * kTileBytes + ((kTabBytes + 15) & ~15) + kPosBytes + kAuxBytes;
   static constexpr int kSmemBytes = kCandBytes + kWarps * kWarpBytes;
+  // the group writer takes block_off / local_off of its first env only: a group must not straddle two count-CTAs
+  static_assert(kEpb % kGroup == 0, "TC_GROUP_D*: the env group of a writer warp must divide the count kernels' envs per CTA");
 };
 
 // TC_TMA_L2_HINT: 0 = none (default), 1 = evict_first, 2 = evict_last, 3 = no_allocate-like evict_first at fraction 0

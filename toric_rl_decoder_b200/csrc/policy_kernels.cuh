@@ -13,7 +13,7 @@
 
 namespace tc {
 
-constexpr uint32_t kDomSelect = 0x40000000u;   // Philox counter word 3 domain of the epsilon-greedy draws
+// kDomSelect (common.cuh): Philox counter word 3 domain of the epsilon-greedy draws
 
 // One warp per env.  Q-values of the env are the rows offsets[e] .. offsets[e+1]-1 of q (float32 [sumP][3]).
 // Greedy: first maximum in row-major (perspective, action) order == np.argmax / np.where(...)[0]
@@ -45,7 +45,7 @@ select_action_kernel(const float* __restrict__ q, const uint8_t* __restrict__ po
   const uint64_t env_id = (uint64_t)(env_base + e);
   const uint32_t ep = episode ? episode[e] : 0u;
   const uint32_t stp = steps ? (uint32_t)steps[e] : 0u;
-  const uint4 rnd = philox4x32_10(make_uint4((uint32_t)env_id, (uint32_t)(env_id >> 32), ep, kDomSelect | stp), key);
+  const uint4 rnd = philox4x32_10(make_uint4((uint32_t)env_id, (uint32_t)(env_id >> 32), ep, kDomSelect | (stp & kSelectStepMask)), key);
   const uint32_t thr = eps_thresh ? eps_thresh[e] : eps_scalar;
   const bool greedy = greedy_in ? (greedy_in[e] != 0) : !(rnd.x < thr);
   int p, a;

@@ -38,8 +38,6 @@
 
 namespace tc {
 
-constexpr uint32_t kDomFirst = 0x40000000u;    // first-error draw of the conditioned sampler
-
 struct SampleStats {
   int attempts;
   int nx, ny, nz;

@@ -247,6 +247,11 @@ __global__ void __launch_bounds__(kThreads) ground_state_kernel(const uint32_t* 
 #define TC_COUNT_THREADS 256
 #endif
 constexpr int kCountThreads = TC_COUNT_THREADS;
+// cta_count_prefix scans the CTA's env counts in ONE warp out of `sc[32]`: at most 32 envs per CTA at the narrowest
+// group (G = 8); whole warps only; and actor_step_kernel's launch bound scales by 256 / kCountThreads
+static_assert(kCountThreads % 32 == 0 && kCountThreads >= 32, "TC_COUNT_THREADS: whole warps");
+static_assert(kCountThreads / 8 <= 32, "TC_COUNT_THREADS: more than 32 envs per CTA overruns cta_count_prefix's scan");
+static_assert(256 % kCountThreads == 0, "TC_COUNT_THREADS must divide 256 (launch bounds of actor_step_kernel)");
 
 template <int G>
 __device__ __forceinline__ void cta_count_prefix(int count, bool valid, int r, int64_t e,
