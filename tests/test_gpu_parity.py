@@ -168,6 +168,78 @@ def test_envset_envs_views(pkg):
     assert (now[keep] == q_all[keep]).all()
 
 
+def test_envset_step_after_state_assignment(pkg):
+    """envs[i].state = X followed by the BATCHED EnvSet.step: env i takes its reward against X and gets its new state
+    from the qubits (ToricCode.py:83-86), exactly as a per-env step would; the other envs take the incremental path;
+    the mark is gone afterwards (the second batched step is incremental for everybody)."""
+    d, n = 5, 6
+    es = pkg.EnvSetB200({"size": d, "p_error": 0.15}, n, seed=9)
+    s0 = es.resetAll()
+    q0 = es.engine.get_qubits().cpu().numpy().astype(np.int64)
+    fake = np.zeros((2, d, d), dtype=np.int64)
+    fake[0, 1, 1] = fake[1, 3, 2] = fake[1, 0, 4] = fake[0, 4, 4] = 1
+    es.envs[4].state = fake
+    es.envs[1].state = np.zeros((2, d, d), dtype=int)
+    rng = np.random.default_rng(21)
+    acts = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)], 1)
+    st, r, term, _ = es.step(acts)
+    start = {4: fake, 1: np.zeros((2, d, d), dtype=np.int64)}
+    q1, s1 = [], []
+    for i in range(n):
+        qi, si, ri, ti = O.step(q0[i], start.get(i, s0[i]), list(acts[i]))
+        assert (st[i] == si).all() and r[i] == ri and term[i] == ti, i
+        q1.append(qi)
+        s1.append(si)
+    assert not es._state_assigned
+    acts2 = np.stack([rng.integers(0, 2, n), rng.integers(0, d, n), rng.integers(0, d, n), rng.integers(1, 4, n)], 1)
+    st2, r2, term2, _ = es.step(acts2)
+    for i in range(n):
+        _, si, ri, ti = O.step(q1[i], s1[i], list(acts2[i]))
+        assert (st2[i] == si).all() and r2[i] == ri and term2[i] == ti, i
+
+
+@pytest.mark.parametrize("kind", ("single", "view"))
+def test_start_from_state_call_sequence(pkg, kind):
+    """The call sequence of results/start_from_state.py:34-58 (reset, createSyndromOpt of a chosen error,
+    assignment of qubit_matrix and state, plotToricCode, step loop) against a ToricCodeB200 and against
+    EnvSet.envs[i]; the network is replaced by "first perspective, operator X" so that the test needs no weights."""
+    d = 5
+    if kind == "single":
+        env = pkg.ToricCodeB200({"size": d, "p_error": 0.1})
+    else:
+        es = pkg.EnvSetB200({"size": d, "p_error": 0.1}, 4, seed=3)
+        es.resetAll()
+        env = es.envs[2]
+    assert env.system_size == d and int(env.action_space.high[-1]) == 3 and env.min_qbit_errors == 0
+    assert env.rule_table[1, 2] == 3 and env.observation_space.shape == (2, d, d)
+    start_error = np.zeros((2, d, d), dtype=int)
+    start_error[0, 1, 2] = 1
+    start_error[1, 3, 3] = 2
+    start_error[0, 4, 0] = 3
+    env.reset()
+    state = env.createSyndromOpt(start_error)
+    assert (state == O.syndrome(start_error)).all()
+    env.qubit_matrix = start_error
+    env.state = state
+    assert env.plotToricCode(state, "step_0") is None
+    q, terminal_state, no_steps = start_error.astype(np.int64), False, 0
+    while not terminal_state and no_steps < 12:
+        _, pos = pkg.generatePerspectiveOptimized(d // 2, d, state)
+        action = [int(pos[0][0]), int(pos[0][1]), int(pos[0][2]), 1]
+        next_state, reward, terminal_state, _ = env.step(action)
+        q, ns, ro, to = O.step(q, state, action)
+        assert (next_state == ns).all() and reward == ro and terminal_state == to
+        assert (env.next_state == ns).all() and (env.qubit_matrix == q).all()
+        state = next_state
+        no_steps += 1
+    # the generators called on their own (ToricCode.py:130-166)
+    m = env.generateRandomError(np.zeros((2, d, d), dtype=int), 0.3)
+    assert m.shape == (2, d, d) and m.min() >= 0 and m.max() <= 3
+    m = env.generateNRandomErrors(np.zeros((2, d, d), dtype=int), 4)
+    assert int((m != 0).sum()) == 4
+    assert (env.qubit_matrix == q).all()                       # neither generator touched the env
+
+
 def test_single_env_api(pkg):
     """ToricCodeB200 mirrors gym_ToricCode's ToricCode, injected with a golden mask."""
     g = golden.per_d(5)

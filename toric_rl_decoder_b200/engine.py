@@ -202,11 +202,11 @@ class ToricEngine:
             idx_t = torch.as_tensor(idx, dtype=torch.int64, device=self.device).contiguous()
             n_idx = idx_t.numel()
             self.steps[idx_t] = 0
-        rng = _Range("toric/reset", self.nvtx)
-        _lib.check(self.lib.tc_reset(_ptr(self.qubits), _ptr(self.syn), _ptr(self.gs), _ptr(self.status),
-                                     _ptr(self.p_thresh), _ptr(self.episode), _ptr(idx_t), n_idx, int(mode),
-                                     int(n_fixed), self.seed, self.env_base, self.d, _stream(self.device)), "tc_reset")
-        rng.__exit__()
+        with _Range("toric/reset", self.nvtx):
+            _lib.check(self.lib.tc_reset(_ptr(self.qubits), _ptr(self.syn), _ptr(self.gs), _ptr(self.status),
+                                         _ptr(self.p_thresh), _ptr(self.episode), _ptr(idx_t), n_idx, int(mode),
+                                         int(n_fixed), self.seed, self.env_base, self.d, _stream(self.device)),
+                       "tc_reset")
         if idx is None:
             self.steps.zero_()
 

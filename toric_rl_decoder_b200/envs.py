@@ -174,7 +174,37 @@ class _EnvView:
 
     def __init__(self, envset, i):
         self._es, self._i = envset, int(i)
-        self.system_size = envset.size
+        d = self.system_size = envset.size
+        self.min_qbit_errors = envset.min_qbit_errors
+        self.action_space = _Box(np.array([0, 0, 0, 0]), np.array([1, d, d, 3]), (4,))
+        self.observation_space = _Box(0, 1, (2, d, d))
+        self.rule_table = np.array([[0, 1, 2, 3], [1, 0, 3, 2], [2, 3, 0, 1], [3, 2, 1, 0]], dtype=int)
+
+    @property
+    def next_state(self):
+        """ToricCode.next_state (ToricCode.py:50,86): the state the env's last step produced (views are made on
+        demand, so the batch keeps it); before any step it is the current state."""
+        ns = self._es._next_states.get(self._i)
+        return self.state if ns is None else ns
+
+    @next_state.setter
+    def next_state(self, s):
+        self._es._next_states[self._i] = np.asarray(s)
+
+    # the generators and the stencil as functions of their arguments (ToricCode.py:130-199): they do not touch this
+    # env, so they run on the batch's one-env helper
+    def createSyndromOpt(self, tcode):
+        return self._es._helper().createSyndromOpt(tcode)
+
+    def generateRandomError(self, matrix, p_error):
+        return self._es._helper().generateRandomError(matrix, p_error)
+
+    def generateNRandomErrors(self, matrix, n):
+        return self._es._helper().generateNRandomErrors(matrix, n)
+
+    def plotToricCode(self, state, title):
+        """No graphics stack -- unavailable on this box (see ToricCodeB200.plotToricCode)."""
+        return None
 
     def _rows(self):
         e, i = self._es.engine, self._i
@@ -240,10 +270,11 @@ class _EnvView:
         if assigned:                  # ToricCode.py:83-86: new state from the qubits, reward against the assigned one
             self._es._state_assigned.discard(i)
             _lib.check(e.lib.tc_syndrome(_ptr(q), _ptr(syn), e.d, 1, _stream(e.device)), "tc_syndrome")
-            st = self.state
+            st = self.next_state = self.state
             after = int(st.sum())
             return st, (100 if after == 0 else before - after), after == 0, {}
-        return self.state, int(e.reward[i].item()), bool(e.terminal[i].item()), {}
+        st = self.next_state = self.state
+        return st, int(e.reward[i].item()), bool(e.terminal[i].item()), {}
 
     def evalGroundState(self):
         e, q, _ = self._rows()
@@ -297,11 +328,20 @@ class EnvSetB200:
         self.engine = ToricEngine(size, self.no_envs, device=device, seed=seed, env_base=env_base, p_error=p)
         self.envs = _EnvList(self)
         self._state_assigned = set()     # envs whose `state` was assigned through envs[i] since their last step / reset
+        self._next_states = {}           # envs[i].next_state of the envs stepped through their view
+        self._one = None                 # one-env helper behind envs[i].createSyndromOpt / generate*Error*
         self.states = self._states()
 
     def _states(self):
         st = self.engine.get_state()
         return st.cpu().numpy().astype(np.int64) if self.numpy_compat else st
+
+    def _helper(self):
+        if self._one is None:
+            e = self.engine
+            self._one = ToricCodeB200({"size": self.size, "min_qbit_errors": self.min_qbit_errors}, device=e.device,
+                                      seed=e.seed, env_base=e.env_base + (1 << 41))     # a Philox stream of its own
+        return self._one
 
     def _reset(self, idx):
         if idx is None:
@@ -334,8 +374,25 @@ class EnvSetB200:
     def step(self, actions):
         """EnvSet.step (src/EnvSet.py:38-47): (states, rewards, terminals, info)."""
         a = torch.as_tensor(np.asarray(actions, dtype=np.int64) if not torch.is_tensor(actions) else actions)
-        reward, terminal = self.engine.step(a)
-        st = self.engine.get_state()
+        e = self.engine
+        assigned = sorted(self._state_assigned)
+        if assigned:                  # defect counts of the states assigned through envs[i].state = ...
+            it = torch.as_tensor(assigned, dtype=torch.int64, device=e.device)
+            before = e.get_state(e.syn[it].contiguous()).flatten(1).sum(1, dtype=torch.float32)
+        reward, terminal = e.step(a)
+        if assigned:
+            # ToricCode.py:83-86 for those envs, as ToricCodeB200.step / _EnvView.step do: the new state is recomputed
+            # from the qubits (the incremental update ran on a state that need not match them), the reward is
+            # taken against the assigned state
+            for i in assigned:
+                _lib.check(e.lib.tc_syndrome(_ptr(e.qubits[i:i + 1]), _ptr(e.syn[i:i + 1]), e.d, 1, _stream(e.device)),
+                           "tc_syndrome")
+            after = e.get_state(e.syn[it].contiguous()).flatten(1).sum(1, dtype=torch.float32)
+            done = after == 0
+            reward[it] = torch.where(done, torch.full_like(after, 100.0), before - after)
+            terminal[it] = done.to(terminal.dtype)
+            self._state_assigned.clear()
+        st = e.get_state()
         if self.numpy_compat:
             return (st.cpu().numpy().astype(np.int64), reward.cpu().numpy().astype(np.float64),
                     terminal.cpu().numpy().astype(bool), {})
