@@ -40,7 +40,14 @@ def parse_args():
                     help="untimed, uncounted steps before --warmup (episode clocks are pre-staggered over "
                          "[0, max_steps], so the timed region sees the stationary reset rate whatever --steps is)")
     ap.add_argument("--no-stagger", action="store_true", help="keep every env's episode clock at 0 after reset")
-    ap.add_argument("--cpu-envs", type=int, default=8192, help="envs in the bounded CPU sample")
+    ap.add_argument("--cpu-envs", type=int, default=0,
+                    help="envs the CPU arm walks per pass; 0 = --envs, the batch the GPU arm steps (one slice per thread)")
+    ap.add_argument("--repeats", type=int, default=5, help="how often the --steps region is timed (value = the first)")
+    ap.add_argument("--kernel-samples", type=int, default=16,
+                    help="least number of event-timed writer launches behind roofline.kernel_ms (a post-region pass "
+                         "on the same stationary state supplies what the timed region did not)")
+    ap.add_argument("--e2e-min-steps", type=int, default=1024,
+                    help="the e2e regions run max(--steps, this) steps (bounded by 1 GiB of pinned actions)")
     ap.add_argument("--ref-step-seconds", type=float, default=0.25,
                     help="--impl reference: CPU time one reference 'step' (a whole number of passes over the "
                          "--cpu-envs sample) is calibrated to")
@@ -57,7 +64,26 @@ def parse_args():
                     help="1: the one-kernel step (TC_ACTOR_SINGLE_PASS), 0: the three-kernel step, -1: the engine's default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.cpu_envs <= 0:
+        a.cpu_envs = a.envs
+    return a
+
+
+NOMINAL_HBM_GBS = 8000.0      # B200 HBM3e nominal, the figure north_star's ">= 60 %" is quoted on
+
+
+def bench_config(a, world):
+    """The `config` object of BOTH arms (the driver compares them): only what the command line fixes.  What a run
+    measures about its workload (perspectives per env, bytes per env-step) goes into `workload_stats`."""
+    return {"workload": workload_name(a), "d": a.d, "p_error": a.p, "envs_per_gpu": a.envs,
+            "global_envs": a.envs * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
+            "out_dtype": a.out_dtype,
+            "regime": ("stationary: episode clocks staggered over [0, 75], untimed burn-in of at least one episode "
+                       "length before the warm-up") if not a.no_stagger else
+                      "all envs start their first episode at the first warm-up step",
+            "l2": "no flush: every step streams a fresh perspective tensor far larger than the 126 MB L2 "
+                  "(bytes per step: workload_stats)"}
 
 
 def workload_name(a):
@@ -236,11 +262,9 @@ def run_reference(a):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-            "data": "synthetic", "config": {"workload": workload_name(a),
-                                            "note": "CPU arm: each step is a bounded sample of the same loop on the "
-                                                    "host cores (%d passes over %d envs)" % (passes, a.cpu_envs),
-                                            "passes_per_step": passes, "cpu_envs": a.cpu_envs},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": loop.nthreads, "kind": "port", "sample": sample},
+            "data": "synthetic", "config": bench_config(a, max(a.gpus, 1)),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": loop.nthreads, "kind": "port", "sample": sample,
+                             "passes_per_step": passes, "cpu_envs": a.cpu_envs},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "nonce": _nonce()}
     print(json.dumps(line), flush=True)
@@ -265,6 +289,9 @@ def run_b200(a):
         import torch.distributed as dist
     dev = torch.device("cuda", local)
     d, n = a.d, a.envs
+    # N > 1: pin the process to the cores next to its GPU BEFORE any pinned host buffer exists, so that eight ranks
+    # downloading at once do it into NUMA-local memory.  Not at N = 1: the cpu_baseline leg of that run needs every core.
+    numa_cpus = sharding.bind_to_gpu_numa(local) if world > 1 else 0
 
     out_dtype = getattr(torch, a.out_dtype)
     esz = torch.empty((), dtype=out_dtype).element_size()
@@ -323,16 +350,49 @@ def run_b200(a):
         ev1.record()
         barrier()
     ms = ev0.elapsed_time(ev1)
-    if one_kernel:          # the step IS the kernel: its launches run back to back, so step time = kernel time
-        write_ms = ms / a.steps
-        sampled_sum_p = float(eng.counters[5].item()) / a.steps
-    else:
-        write_ms = sum(evb[k].elapsed_time(evc[k]) for k in sampled) / len(sampled)
-        sampled_sum_p = float(totals.sum().item()) / len(sampled)
+    ctr = eng.counters.clone()                             # the counters of the region `value` is quoted on
+    sum_p_local = int(ctr[5].item())
     per_launch_sum_p = [int(x) for x in totals.tolist()] if a.dump_launches else None
-    ctr = eng.counters.clone()
-    assert int(eng.overflow.item()) == 0
     ms = sharding.max_over_ranks(ms, dev)                  # time = max over ranks
+
+    # the same region again (same stationary state, it just keeps running): run-to-run spread of `value`
+    repeat_ms = [ms]
+    for _ in range(max(a.repeats, 1) - 1):
+        barrier()
+        ev0.record()
+        for k in range(a.steps):
+            eng.actor_step()
+        ev1.record()
+        barrier()
+        repeat_ms.append(sharding.max_over_ranks(ev0.elapsed_time(ev1), dev))
+
+    # writer-launch samples: those of the timed region plus a post-region pass in the split form until there are
+    # at least --kernel-samples of them, whatever --steps was
+    if one_kernel:          # the step IS the kernel: its launches run back to back, so step time = kernel time
+        launch_ms = [ms / a.steps]
+        sampled_sum_p = float(sum_p_local) / a.steps
+        n_launches = a.steps
+    else:
+        launch_ms = [evb[k].elapsed_time(evc[k]) for k in sampled]
+        launch_sum_p = [int(x) for x in totals.tolist()][:len(sampled)]
+        extra = max(a.kernel_samples - len(sampled), 0)
+        xb = [torch.cuda.Event(enable_timing=True) for _ in range(extra)]
+        xc = [torch.cuda.Event(enable_timing=True) for _ in range(extra)]
+        xtot = torch.zeros(max(extra, 1), dtype=torch.int64, device=dev)
+        for k in range(extra):
+            eng.actor_pre()
+            xb[k].record()
+            eng.persp_write()
+            xc[k].record()
+            xtot[k].copy_(eng.offsets[n], non_blocking=True)
+        torch.cuda.synchronize()
+        launch_ms += [xb[k].elapsed_time(xc[k]) for k in range(extra)]
+        launch_sum_p += [int(x) for x in xtot.tolist()][:extra]
+        sampled_sum_p = float(sum(launch_sum_p)) / len(launch_sum_p)
+        n_launches = len(launch_ms)
+    write_ms = sum(launch_ms) / len(launch_ms)
+    srt = sorted(launch_ms)
+    assert int(eng.overflow.item()) == 0
     sharding.allreduce_counters(ctr)                       # the path's only collective: counter all-reduce
     c = {name: int(ctr[i].item()) for i, name in enumerate(pkg.engine.COUNTER_NAMES)}
     total_steps = c["env_steps"]
@@ -340,7 +400,6 @@ def run_b200(a):
     if not a.no_stagger and a.steps >= 8:
         assert c["episodes"] > 0, "the timed region saw no episode end: not the stationary regime"
     value = total_steps / (ms * 1e-3)
-    sum_p_local = int(eng.counters[5].item())
     p_bar = sum_p_local / float(n * a.steps)
 
     peak, peak_src = load_peaks()
@@ -353,9 +412,16 @@ def run_b200(a):
                 # the kernel is a write-only stream and `peak` is a COPY (read+write) figure, so frac can exceed 1;
                 # write_peak is the write-only ceiling measured live (cudaMemsetAsync / float32 fill, best of 6)
                 "write_peak": write_peak, "frac_of_write_peak": achieved / write_peak if write_peak else None,
-                "kernel_ms": write_ms, "kernel_share_of_step": write_ms * a.steps / ms,
-                "kernel_launches_timed": a.steps if one_kernel else len(sampled),
-                "step_achieved": b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9}
+                "nominal": NOMINAL_HBM_GBS, "frac_of_nominal": achieved / NOMINAL_HBM_GBS,
+                "kernel_ms": write_ms, "kernel_ms_min": srt[0], "kernel_ms_median": srt[len(srt) // 2],
+                "kernel_ms_max": srt[-1], "kernel_share_of_step": write_ms * a.steps / ms,
+                "kernel_launches_timed": n_launches,
+                "kernel_launches_in_region": a.steps if one_kernel else len(sampled)}
+    step_achieved = b_alg(d, n, sum_p_local / a.steps, esz) / (ms / a.steps * 1e-3) / 1e9
+    roofline["step_achieved"] = step_achieved
+    roofline["step_frac"] = {"of_measured_copy_peak": step_achieved / peak,
+                             "of_write_peak": step_achieved / write_peak if write_peak else None,
+                             "of_nominal": step_achieved / NOMINAL_HBM_GBS}
     if per_launch_sum_p is not None:
         roofline["timed_launch_steps"] = sampled
         roofline["timed_launch_sum_p"] = per_launch_sum_p
@@ -375,7 +441,7 @@ def run_b200(a):
             pass
 
     # ---- e2e: reference-facing call with HOST buffers (actions in, step results out) ----------
-    e2e = e2e_open = e2e_u8 = None
+    e2e = e2e_open = e2e_rows = None
     if not a.no_e2e:
         del eng
         torch.cuda.empty_cache()
@@ -385,10 +451,21 @@ def run_b200(a):
                                 **ekw)
             e.ensure_capacity(e.worst_case_capacity())
             return e
-        recorded = record_device_policy(a, make_engine, max(3, a.warmup) + a.steps)
-        e2e = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 1)
-        e2e_open = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 3)
-        e2e_u8 = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "u8", 1)
+        # long enough to be a measurement of its own (>= a few hundred ms at the BENCH config), bounded by 1 GiB of
+        # pinned recorded actions
+        e2e_steps = max(a.steps, min(a.e2e_min_steps, (1 << 30) // (n * 16)))
+        recorded = record_device_policy(a, make_engine, max(3, a.warmup) + e2e_steps)
+        # `e2e` is the reference's own host contract: EnvSet.step hands back the uint8 (n,2,d,d) states, one byte per
+        # stabiliser, every step (src/EnvSet.py:38-47) -- that array is downloaded whole.  The cheaper host formats
+        # (row-packed states behind a LazyStates view; three steps in flight) are reported under their own keys.
+        e2e = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "u8", 1, e2e_steps)
+        e2e_rows = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 1, e2e_steps)
+        e2e_open = run_e2e(a, make_engine, recorded, dev, dist, barrier, world, "lazy", 3, e2e_steps)
+        if world > 1:
+            for o in (e2e, e2e_rows, e2e_open):
+                o["numa_bound_cpus"] = numa_cpus
+            e2e["limit"] = ("host D->H rate: %d ranks x %.1f MB per step into one host's memory"
+                            % (world, e2e["d2h_bytes_per_step"] / 1e6))
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
@@ -401,17 +478,14 @@ def run_b200(a):
                 "vs_baseline": None, "dtype": "u32 bit planes -> %s" % {"float32": "f32", "bfloat16": "bf16",
                                                                         "float16": "f16", "uint8": "u8"}[a.out_dtype],
                 "data": "synthetic",
-                "config": {"workload": workload_name(a), "d": d, "p_error": a.p, "envs_per_gpu": n,
-                           "global_envs": n * world, "parallelism": "env-sharded x%d, no data-path collective" % world,
-                           "mean_perspectives_per_env": p_bar, "out_dtype": a.out_dtype,
-                           "regime": ("stationary: episode clocks staggered over [0, %d], %d untimed burn-in steps "
-                                      "before the warm-up" % (max_steps, a.burnin)) if not a.no_stagger else
-                                     "all envs start their first episode at the first warm-up step",
-                           "l2": "no flush needed: each step streams %.2f GB of new output (>> 126 MB L2)"
-                                 % (wbytes / 1e9),
-                           "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_open_loop": e2e_open,
-                "e2e_u8_full": e2e_u8,
+                "config": bench_config(a, world),
+                "workload_stats": {"mean_perspectives_per_env": p_bar, "burnin_steps": a.burnin,
+                                   "max_steps_per_episode": max_steps,
+                                   "writer_bytes_per_step": wbytes,
+                                   "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
+                "value_repeats": [n * a.steps * world / (m * 1e-3) for m in repeat_ms],
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_rows": e2e_rows,
+                "e2e_open_loop": e2e_open,
                 "gpu_launches": (1 if one_kernel else 3) * a.steps,
                 "step_form": "single-pass (1 kernel)" if one_kernel else "three kernels (step+count, scan, writer)",
                 "clocks": clk.summary(), "nonce": _nonce(),
@@ -479,7 +553,7 @@ def record_device_policy(a, make_engine, total_steps):
     return host, sum_p
 
 
-def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
+def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth, steps):
     """Same metric through the host-facing call (toric_rl_decoder_b200.HostActorPipeline): every step copies
     that step's actions (n,4) int32 from pinned host memory, runs the fused actor step, and reads rewards,
     terminals, perspective counts and the new states back to pinned host memory; every step's results are read
@@ -492,11 +566,11 @@ def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
     the writer of the same step.  depth=3 (`e2e_open_loop`) keeps three steps in flight, i.e. no action depends
     on a downloaded result.
 
-    states="lazy" (`e2e`, `e2e_open_loop`): the states cross PCIe row-packed (ceil(d/8) bytes per lattice row)
+    states="u8" (`e2e`, the headline): the reference's own contract -- the one-byte-per-stabiliser (n,2,d,d) array is
+    expanded on the device and downloaded whole every step; at 8 ranks the box's aggregate device->host rate
+    (~90 GB/s, profiles/r01_e2e_scale_probe.txt), not the GPUs, bounds that form.
+    states="lazy" (`e2e_rows`, `e2e_open_loop`): the states cross PCIe row-packed (ceil(d/8) bytes per lattice row)
     and the host sees the reference's (n,2,d,d) array as a LazyStates view that expands only the envs it indexes.
-    states="u8" (`e2e_u8_full`): the one-byte-per-stabiliser array is expanded on the device and downloaded whole
-    every step -- at 8 ranks the box's aggregate device->host rate (~90 GB/s,
-    profiles/r01_e2e_scale_probe.txt), not the GPUs, bounds that form.
 
     The host policy replays the actions the device's random policy chose on the same seed (recorded beforehand,
     record_device_policy), so the envs walk exactly the trajectory `value` was timed on -- same resets, same
@@ -506,7 +580,7 @@ def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
     from toric_rl_decoder_b200 import HostActorPipeline, sharding
     n = a.envs
     host_actions, rec_sum_p = recorded
-    warm = host_actions.shape[0] - a.steps
+    warm = host_actions.shape[0] - steps
     eng = make_engine()
     prepare(a, eng)
     pipe = HostActorPipeline(eng, depth=depth, states=states)
@@ -536,7 +610,7 @@ def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()
-    run(warm, warm + a.steps)
+    run(warm, warm + steps)
     ev1.record()
     torch.cuda.synchronize()
     wall_ms = 1e3 * (time.perf_counter() - t0)
@@ -545,11 +619,11 @@ def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth):
     ms = sharding.max_over_ranks(ms_raw, dev)
     dc = eng.counters - c0
     assert int(eng.counters[5].item()) == rec_sum_p[-1], "host-buffer run left the recorded trajectory"
-    out = {"value": n * world * a.steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
-           "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / a.steps,
+    out = {"value": n * world * steps / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes,
+           "d2h_bytes_per_step": pipe.d2h_bytes, "ms_per_step": ms / steps, "steps": steps,
            "elapsed_ms_raw": ms_raw, "wall_ms": wall_ms, "nonce": _nonce(),
            "steps_in_flight": depth, "loop": "closed" if depth == 1 else "open",
-           "mean_perspectives_per_env": float(dc[5].item()) / float(n * a.steps),
+           "mean_perspectives_per_env": float(dc[5].item()) / float(n * steps),
            "episodes": int(dc[1].item()),
            "call": "HostActorPipeline(depth=%d, states=%r).submit(pinned host actions) / collect() -> host reward, "
                    "terminal, counts, %s; uploads and downloads on their own streams; %s"

@@ -24,13 +24,29 @@ def _check(line, n_gpus):
     assert j["e2e"] == {"value": j["value"], "unit": j["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 
-def test_reference_arm_single_process():
+def _bench_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_under_test", os.path.join(ROOT, "bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_reference_arm_single_process(monkeypatch):
     res = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2",
                           "--warmup", "1", "--cpu-envs", "512"], capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert res.returncode == 0, res.stderr[-2000:]
     lines = [l for l in res.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
     _check(lines[0], 1)
+    # both arms print the SAME config object for the same command line (the driver compares them): it is built by one
+    # function from the arguments alone, and the size of the CPU sample is not part of it
+    bench = _bench_module()
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--steps", "2", "--warmup", "1"])
+    a = bench.parse_args()
+    assert a.cpu_envs == a.envs == 65536                    # by default the CPU arm walks the batch the GPU arm steps
+    assert json.loads(lines[0])["config"] == bench.bench_config(a, 1)
+    assert "cpu_envs" in json.loads(lines[0])["cpu_baseline"]
 
 
 def test_reference_arm_under_torchrun_two_ranks():
