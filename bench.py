@@ -62,6 +62,9 @@ def parse_args():
                          "(to match an ncu capture of one launch of the same command, scripts/gpu_traffic.sh)")
     ap.add_argument("--single-pass", type=int, default=-1, choices=(-1, 0, 1),
                     help="1: the one-kernel step (TC_ACTOR_SINGLE_PASS), 0: the three-kernel step, -1: the engine's default")
+    ap.add_argument("--ref-api-steps", type=int, default=8,
+                    help="timed iterations of the reference actor's loop body through the reference-named mirrors "
+                         "(e2e_reference_api, N = 1 only); 0 = skip")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     a = ap.parse_args()
@@ -166,7 +169,7 @@ class ClockSampler:
 
     def summary(self):
         return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
-                "reasons": sorted(self.reasons), "samples": len(self.sm), "how": "NVML, 2 ms period, timed region only"}
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "how": "NVML, 2 ms period, over the timed region and its repeats"}
 
 
 def load_peaks():
@@ -349,22 +352,23 @@ def run_b200(a):
                 eng.actor_step()           # the same three kernels, one call
         ev1.record()
         barrier()
-    ms = ev0.elapsed_time(ev1)
-    ctr = eng.counters.clone()                             # the counters of the region `value` is quoted on
-    sum_p_local = int(ctr[5].item())
-    per_launch_sum_p = [int(x) for x in totals.tolist()] if a.dump_launches else None
-    ms = sharding.max_over_ranks(ms, dev)                  # time = max over ranks
+        ms = ev0.elapsed_time(ev1)
+        ctr = eng.counters.clone()                             # the counters of the region `value` is quoted on
+        sum_p_local = int(ctr[5].item())
+        per_launch_sum_p = [int(x) for x in totals.tolist()] if a.dump_launches else None
+        ms = sharding.max_over_ranks(ms, dev)                  # time = max over ranks
 
-    # the same region again (same stationary state, it just keeps running): run-to-run spread of `value`
-    repeat_ms = [ms]
-    for _ in range(max(a.repeats, 1) - 1):
-        barrier()
-        ev0.record()
-        for k in range(a.steps):
-            eng.actor_step()
-        ev1.record()
-        barrier()
-        repeat_ms.append(sharding.max_over_ranks(ev0.elapsed_time(ev1), dev))
+        # the same region again (same stationary state, it just keeps running): run-to-run spread of `value`; the
+        # clock sampler stays on, so that a short --steps region still gets more than a couple of NVML samples
+        repeat_ms = [ms]
+        for _ in range(max(a.repeats, 1) - 1):
+            barrier()
+            ev0.record()
+            for k in range(a.steps):
+                eng.actor_step()
+            ev1.record()
+            barrier()
+            repeat_ms.append(sharding.max_over_ranks(ev0.elapsed_time(ev1), dev))
 
     # writer-launch samples: those of the timed region plus a post-region pass in the split form until there are
     # at least --kernel-samples of them, whatever --steps was
@@ -467,6 +471,15 @@ def run_b200(a):
             e2e["limit"] = ("host D->H rate: %d ranks x %.1f MB per step into one host's memory"
                             % (world, e2e["d2h_bytes_per_step"] / 1e6))
 
+    ref_api = None
+    if world == 1 and a.ref_api_steps > 0 and not a.no_e2e:
+        ref_api = {"loop": "src/Actor_mp.py:104-183 literally, network replaced by a uniformly random perspective and "
+                           "operator: generatePerspectiveBatch(state) -> tc_select_action(epsilon=1) -> EnvSet.step -> "
+                           "generateTransitionParallel -> resetTerminalEnvs(idx, p_errors) -> next_state[idx] = "
+                           "reset_states; wall clock around the loop, device idle at both ends",
+                   "numpy_compat_true": run_reference_api(a, dev, True, a.ref_api_steps),
+                   "numpy_compat_false": run_reference_api(a, dev, False, a.ref_api_steps)}
+
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         cpu = cpu_arm(a, a.cpu_seconds, a.cpu_envs)
@@ -485,7 +498,7 @@ def run_b200(a):
                                    "b_alg_bytes_per_env_step": b_alg(d, n, sum_p_local / a.steps, esz) / n},
                 "value_repeats": [n * a.steps * world / (m * 1e-3) for m in repeat_ms],
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "e2e_rows": e2e_rows,
-                "e2e_open_loop": e2e_open,
+                "e2e_open_loop": e2e_open, "e2e_reference_api": ref_api,
                 "gpu_launches": (1 if one_kernel else 3) * a.steps,
                 "step_form": "single-pass (1 kernel)" if one_kernel else "three kernels (step+count, scan, writer)",
                 "clocks": clk.summary(), "nonce": _nonce(),
@@ -640,6 +653,67 @@ def run_e2e(a, make_engine, recorded, dev, dist, barrier, world, states, depth, 
     del pipe, eng
     torch.cuda.empty_cache()
     return out
+
+
+def run_reference_api(a, dev, numpy_compat, steps, warm=2):
+    """The loop body of the reference's actor (src/Actor_mp.py:104-183) through the mirrors that carry the
+    reference's names, as a reference user would write it after changing only the imports: numpy `state` in,
+    `EnvSetB200.step`, `generateTransitionParallel`, `resetTerminalEnvs`, `next_state[idx] = reset_states`.  The
+    Q-network is left out (a uniformly random perspective and operator are drawn instead, by tc_select_action with
+    epsilon = 1 over a zero Q table), everything else is the reference's sequence.
+
+    numpy_compat=True hands the caller the reference's dtypes: every step converts 65 536 x 98 stabilisers to int64
+    on the host twice over (EnvSet.step's states, 51 MB, and the transition records, 2 x 51 MB) -- that conversion,
+    single-threaded numpy, is the bound of this form, not the GPU.  numpy_compat=False keeps states, rewards and
+    terminals on the device as tensors; the states still make the round trip device -> uint8 tensor -> pack ->
+    perspectives that the array-in / array-out signatures imply."""
+    import numpy as np
+    import torch
+    import toric_rl_decoder_b200 as pkg
+    d, n, g = a.d, a.envs, a.d // 2
+    es = pkg.EnvSetB200({"size": d, "p_error": a.p}, n, device=dev, seed=a.seed, numpy_compat=numpy_compat)
+    trans_type = pkg.transition_type(d) if numpy_compat else None
+    state = es.resetAll()
+    max_actions = 75
+    if numpy_compat:
+        steps_per_episode = stagger_clocks(np.arange(n), max_actions).astype(np.int64)
+    else:
+        steps_per_episode = torch.from_numpy(stagger_clocks(np.arange(n), max_actions).astype(np.int64)).to(dev)
+    sum_p = resets = 0
+    t0 = 0.0
+    for k in range(warm + steps):
+        if k == warm:
+            torch.cuda.synchronize()
+            sum_p = resets = 0
+            t0 = time.perf_counter()
+        steps_per_episode += 1
+        persp, pos, counts, offsets = pkg.generatePerspectiveBatch(g, d, state, device=dev, raw_positions=True)
+        q = torch.zeros((persp.shape[0], 3), dtype=torch.float32, device=dev)
+        step_no = torch.full((n,), k, dtype=torch.int32, device=dev)
+        act, q_values = pkg.select_action_device(q, pos, offsets, n, epsilon=1.0, steps=step_no, seed=a.seed)
+        action = act.cpu().numpy().astype(np.int64) if numpy_compat else act
+        next_state, reward, terminal_state, _ = es.step(action)
+        transition = pkg.generateTransitionParallel(action, reward, state, next_state, terminal_state, g, trans_type,
+                                                    device=dev)
+        del transition
+        too_many_steps = steps_per_episode > max_actions
+        if numpy_compat:
+            idx = np.argwhere(np.logical_or(terminal_state, too_many_steps)).flatten()
+        else:
+            idx = torch.nonzero(terminal_state | too_many_steps).flatten()
+        if len(idx):
+            p_errors = np.full(len(idx), a.p) if numpy_compat else None
+            reset_states = es.resetTerminalEnvs(idx, p_errors=p_errors)
+            next_state[idx] = reset_states
+            steps_per_episode[idx] = 0
+        sum_p += int(persp.shape[0])
+        resets += int(len(idx))
+        state = next_state
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return {"value": n * steps / dt, "unit": UNIT, "ms_per_step": 1e3 * dt / steps, "steps": steps, "warmup": warm,
+            "mean_perspectives_per_env": sum_p / float(n * steps), "resets_per_step": resets / float(steps),
+            "host_conversion_bytes_per_step": (3 * n * 2 * d * d * 8) if numpy_compat else 0}
 
 
 def main():

@@ -346,7 +346,7 @@ class EnvSetB200:
     def _reset(self, idx):
         if idx is None:
             self._state_assigned.clear()
-        else:
+        elif self._state_assigned:
             self._state_assigned.difference_update(int(i) for i in np.asarray(idx).reshape(-1))
         if self.min_qbit_errors == 0:
             self.engine.reset(idx, mode=SAMPLE_DEPOLARIZING)
@@ -363,11 +363,15 @@ class EnvSetB200:
 
     def resetTerminalEnvs(self, idx, p_errors=None):
         """EnvSet.resetTerminalEnvs (src/EnvSet.py:19-26): returns float64 states of the listed envs."""
-        idx = np.asarray(idx, dtype=np.int64).reshape(-1)
+        if torch.is_tensor(idx):                # numpy_compat=False callers keep the index list on the device
+            it = idx.to(device=self.engine.device, dtype=torch.int64).reshape(-1)
+            idx = it.cpu().numpy() if (p_errors is not None or self._state_assigned) else it
+        else:
+            idx = np.asarray(idx, dtype=np.int64).reshape(-1)
+            it = torch.as_tensor(idx, device=self.engine.device)
         if p_errors is not None:
             self.engine.set_p_error(np.asarray(p_errors, dtype=np.float64), idx=idx)
         self._reset(idx)
-        it = torch.as_tensor(idx, device=self.engine.device)
         st = self.engine.get_state(self.engine.syn[it].contiguous())
         return st.cpu().numpy().astype(np.float64) if self.numpy_compat else st
 

@@ -143,7 +143,8 @@ def generateTransitionParallel(action, reward, state, next_state, terminal_state
         raise ValueError("grid_shift must be toric_size // 2")
     dev = torch.device(device)
     sp, sn = _pack(state, d, dev), _pack(next_state, d, dev)
-    act = torch.as_tensor(np.asarray(action, dtype=np.int64)).to(device=dev, dtype=torch.int32).contiguous()
+    act = action if torch.is_tensor(action) else torch.as_tensor(np.asarray(action, dtype=np.int64))
+    act = act.to(device=dev, dtype=torch.int32).contiguous()
     op, on, ao = transitions_device(sp, sn, act, d, out_dtype=torch.uint8)
     if trans_type is None:
         return op, ao, reward, on, terminal_state
@@ -154,9 +155,9 @@ def generateTransitionParallel(action, reward, state, next_state, terminal_state
     aon = ao.cpu().numpy()
     res[names[1]]['position'] = aon[:, :3]
     res[names[1]]['op'] = aon[:, 3]
-    res[names[2]] = np.asarray(reward)
+    res[names[2]] = reward.cpu().numpy() if torch.is_tensor(reward) else np.asarray(reward)
     res[names[3]] = on.cpu().numpy()
-    res[names[4]] = np.asarray(terminal_state)
+    res[names[4]] = terminal_state.cpu().numpy() if torch.is_tensor(terminal_state) else np.asarray(terminal_state)
     return res
 
 
