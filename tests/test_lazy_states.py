@@ -39,3 +39,40 @@ def test_lazy_states_copy_detaches():
 def test_lazy_states_empty_batch():
     _, lazy = _pair(0, 5, 0)
     assert np.asarray(lazy).shape == (0, 2, 5, 5) and lazy[0:0].shape == (0, 2, 5, 5)
+
+
+@pytest.mark.parametrize("d", (3, 7, 9, 17))
+def test_lazy_states_assignment_follows_numpy(d):
+    """Item assignment on the view (the reference's `next_state[idx] = reset_states`, src/Actor_mp.py:182) gives
+    what the same assignment gives on the expanded array, and never writes through to the download slot."""
+    from toric_rl_decoder_b200.hostpipe import LazyStates
+    rng = np.random.default_rng(d)
+    n = 23
+    full = (rng.random((n, 2, d, d)) < 0.3).astype(np.uint8)
+    slot = np.packbits(full, axis=-1, bitorder="little")
+    slot_before = slot.copy()
+    view = LazyStates(slot, d)
+    ref = full.astype(np.int64)
+    idx = np.array([1, 5, 6, 20])
+    reset_states = (rng.random((4, 2, d, d)) < 0.4).astype(np.float64)          # resetTerminalEnvs returns float64
+    view[idx] = reset_states
+    ref[idx] = reset_states
+    assert (np.asarray(view) == ref).all() and (slot == slot_before).all()
+    mask = rng.random(n) < 0.5
+    view[mask] = 0
+    ref[mask] = 0
+    view[3] = np.ones((2, d, d))
+    ref[3] = 1
+    view[2:9:3, 1] = 1
+    ref[2:9:3, 1] = 1
+    view[7, 0, 1, 2] = 1
+    ref[7, 0, 1, 2] = 1
+    view[idx, 1, :, 0] = np.array([0, 1, 0, 1])[:, None]
+    ref[idx, 1, :, 0] = np.array([0, 1, 0, 1])[:, None]
+    assert (np.asarray(view) == ref).all() and (view[idx] == ref[idx]).all()
+    assert (slot == slot_before).all()
+    c = view.copy()
+    c[0] = 1 - ref[0]
+    assert (np.asarray(view) == ref).all()
+    view[...] = 0
+    assert not np.asarray(view).any()

@@ -40,8 +40,9 @@ class LazyStates:
     dtype = np.dtype(np.uint8)
     ndim = 4
 
-    def __init__(self, rows, d):
+    def __init__(self, rows, d, owned=False):
         self._rows, self._d = rows, int(d)
+        self._owned = bool(owned)          # False: `rows` aliases a pipeline download slot and must not be written
         self.shape = (rows.shape[0], 2, self._d, self._d)
 
     def __len__(self):
@@ -68,8 +69,30 @@ class LazyStates:
     def astype(self, dtype):
         return np.asarray(self).astype(dtype)
 
+    def __setitem__(self, idx, value):
+        """`next_state[idx] = reset_states` (src/Actor_mp.py:182) and numpy's other assignment forms.  The first
+        write detaches the view from the pipeline's download slot (one copy of the packed rows, 1/7 of the expanded
+        array at d=7); the assigned envs are stored packed again, any non-zero value counting as a defect."""
+        if not self._owned:
+            self._rows = self._rows.copy()
+            self._owned = True
+        first, rest = (idx[0], idx[1:]) if isinstance(idx, tuple) and len(idx) else (idx, ())
+        if first is Ellipsis or (isinstance(idx, tuple) and not len(idx)):
+            full = np.asarray(self)
+            full[idx] = np.asarray(value) != 0
+            self._rows[...] = np.packbits(full, axis=-1, bitorder="little")
+            return
+        if not rest:
+            sub = np.empty(self._rows[first].shape[:-1] + (self._d,), dtype=np.uint8)
+            sub[...] = np.asarray(value) != 0
+        else:
+            sub = self._expand(self._rows[first])
+            key = tuple(rest) if isinstance(first, (int, np.integer)) else (slice(None),) + tuple(rest)
+            sub[key] = np.asarray(value) != 0
+        self._rows[first] = np.packbits(sub, axis=-1, bitorder="little")
+
     def copy(self):
-        return LazyStates(self._rows.copy(), self._d)
+        return LazyStates(self._rows.copy(), self._d, owned=True)
 
     @property
     def packed_rows(self):
