@@ -38,6 +38,17 @@ def _engine(d, n, device):
     return eng
 
 
+def _as_defect_bytes(st, dev):
+    """One byte per stabiliser on `dev`, any non-zero byte meaning "defect" (tc_pack_state tests != 0 itself).  A
+    uint8 / bool tensor that already lives there -- what EnvSetB200(numpy_compat=False) hands out -- is used as it is;
+    anything else is compared with 0 first (int64 / float64 arrays of the reference's dtypes: wider than a byte)."""
+    if st.dtype in (torch.uint8, torch.bool) and st.device == dev and st.is_contiguous():
+        return st.view(torch.uint8) if st.dtype is torch.bool else st
+    if st.dtype in (torch.uint8, torch.bool):
+        return st.to(device=dev).contiguous().view(torch.uint8)
+    return (st != 0).to(device=dev, dtype=torch.uint8).contiguous()
+
+
 def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda", raw_positions=False):
     """states: (N,2,d,d) array/tensor of 0/1.  Returns (perspectives f32 (sumP,2,d,d) cuda tensor,
     positions int64 (sumP,3) cuda tensor, counts int32 (N,), offsets int64 (N+1,)).  raw_positions=True keeps
@@ -55,8 +66,8 @@ def generatePerspectiveBatch(grid_shift, toric_size, states, device="cuda", raw_
     n = st.shape[0]
     eng = _engine(d, n, device)
     dev = eng.device
-    syn = torch.zeros((n, 2, d), dtype=torch.int32, device=dev)
-    u8 = (st != 0).to(device=dev, dtype=torch.uint8).contiguous()
+    syn = torch.empty((n, 2, d), dtype=torch.int32, device=dev)        # tc_pack_state writes every word
+    u8 = _as_defect_bytes(st, dev)
     with torch.cuda.device(dev):
         _lib.check(eng.lib.tc_pack_state(_ptr(u8), _ptr(syn), d, n, _stream(dev)), "tc_pack_state")
         eng.perspectives_count(syn=syn, n=n)

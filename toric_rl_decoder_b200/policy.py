@@ -99,7 +99,8 @@ def transitions_device(syn_prev, syn_next, actions, d, out_dtype=torch.float32):
 def _pack(states, d, dev):
     lib = _lib.load()
     st = torch.as_tensor(np.ascontiguousarray(states) if isinstance(states, np.ndarray) else states)
-    u8 = (st != 0).to(device=dev, dtype=torch.uint8).contiguous()
+    from .perspectives import _as_defect_bytes
+    u8 = _as_defect_bytes(st, torch.device(dev))
     syn = torch.empty((u8.shape[0], 2, d), dtype=torch.int32, device=dev)
     _lib.check(lib.tc_pack_state(_ptr(u8), _ptr(syn), d, u8.shape[0], _stream()), "tc_pack_state")
     return syn
