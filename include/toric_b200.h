@@ -45,7 +45,9 @@ extern "C" {
 
 /* flags of tc_actor_step */
 #define TC_ACTOR_RANDOM_ACTIONS 1 /* draw the action on device (uniform over the perspective list x {X,Y,Z}) */
-#define TC_ACTOR_AUTO_RESET 2     /* reset envs that are terminal or past max_steps (Actor_mp.py:171-183) */
+#define TC_ACTOR_AUTO_RESET 2     /* reset envs that are terminal or past max_steps (Actor_mp.py:171-175,181-183) with
+                                   * the env's current p_thresh; the p_error curriculum of :176-180 is
+                                   * tc_p_error_curriculum, run after the step */
 #define TC_ACTOR_FREEZE_DONE 4    /* leave already-solved envs untouched (batched evaluation.py:79 loop exit) */
 #define TC_ACTOR_SINGLE_PASS 8    /* tc_actor_step only: ONE kernel (step + cross-env scan by decoupled look-back +
                                    * perspective writer) instead of three; same results bit for bit.  d <=
@@ -242,6 +244,20 @@ int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* o
                      const int32_t* steps, const uint32_t* eps_thresh, uint32_t eps_scalar,
                      const uint8_t* greedy_in, uint64_t seed, int64_t env_base, int32_t* actions, float* q_sel,
                      int64_t* sel_idx, uint8_t* was_greedy, int64_t n, void* stream);
+
+/* The actor's p_error curriculum (src/Actor_mp.py:43-47,171-181; Distributed_mp.py:53-56,186-189) without leaving the
+ * device.  All probabilities are thresholds floor(p * 2^32).  For every env that was auto-reset by the fused step just
+ * before (steps[e] == 0; all_envs != 0: every env -- call once that way after the initial reset to prime):
+ *   p_cap[e]    <- min(final, p_cap[e] + delta)                                   (:176; p_cap starts at `start`, :47)
+ *   p_thresh[e] <- p_cap[e]                                       'linear'        (:180)
+ *               or uniform on the integers [min(start, cap), cap] 'random'        (:178), drawn as
+ *                  lo + mulhi(Philox(seed; env_base+e, episode[e], 0xA0000000).x, cap - lo + 1)
+ * p_thresh[e] is what the env's NEXT auto-reset samples with: its k-th reset sees the reference's k-th ceiling, chosen
+ * one episode early, so the fused step itself does not change.  steps int32 [n], episode uint32 [n] (read);
+ * p_cap, p_thresh uint32 [n] (read and written). */
+int tc_p_error_curriculum(const int32_t* steps, const uint32_t* episode, uint32_t* p_cap, uint32_t* p_thresh,
+                           uint32_t start_thresh, uint32_t delta_thresh, uint32_t final_thresh, int random_strategy,
+                           int all_envs, uint64_t seed, int64_t env_base, int64_t n, void* stream);
 
 /* generateTransitionParallel's state pair (src/util_actor.py:223-264): both syndromes rolled so the acted
  * qubit sits at (g,g) (shift_state, src/util.py:97-102) and rotated when it lives in matrix 1

@@ -263,3 +263,27 @@ def predict_max(q_values_table, offsets):
             seg = np.concatenate((seg, np.zeros(1, np.float32)))
         out[e] = seg.max()
     return out
+
+
+def p_error_curriculum(steps, episode, p_cap, p_thresh, start_t, delta_t, final_t, random, all_envs, seed, env_base=0):
+    """The reference actor's p_error schedule (src/Actor_mp.py:171-181) in threshold units floor(p * 2^32), as
+    csrc/policy_kernels.cuh:p_error_curriculum_kernel applies it after a fused step: the envs that were just reset
+    (steps == 0; all_envs: every env) get ceiling <- min(final, ceiling + delta) (:176) and the p of their next
+    reset = the ceiling ('linear', :180) or a uniform integer on [min(start, ceiling), ceiling] ('random', :178) drawn
+    as lo + mulhi(Philox(env id, episode, 0xA0000000).x, ceiling - lo + 1).  Returns new (p_cap, p_thresh) uint32."""
+    from . import c_oracle as C
+    cap = np.asarray(p_cap, dtype=np.uint64).copy()
+    thr = np.asarray(p_thresh, dtype=np.uint64).copy()
+    who = np.arange(len(cap)) if all_envs else np.nonzero(np.asarray(steps) == 0)[0]
+    key = (int(seed) & 0xffffffff, int(seed) >> 32)
+    for e in who:
+        c = min(int(final_t), int(cap[e]) + int(delta_t))
+        cap[e] = c
+        p = c
+        if random:
+            lo = min(int(start_t), c)
+            g = int(env_base) + int(e)
+            u = int(C.philox((g & 0xffffffff, g >> 32, int(episode[e]) & 0xffffffff, 0xA0000000), key)[0])
+            p = lo + ((u * (c - lo + 1)) >> 32)
+        thr[e] = p
+    return cap.astype(np.uint32), thr.astype(np.uint32)

@@ -50,6 +50,7 @@ SIGNATURES = {
                       _vp, _vp, _vp, _vp, _vp, _i64, _vp, _sz, _i, _i64, _vp],
     "tc_host_actor_step": [_c.POINTER(HostStep)],
     "tc_select_action": [_vp, _vp, _vp, _vp, _vp, _vp, _c.c_uint32, _vp, _u64, _i64, _vp, _vp, _vp, _vp, _i64, _vp],
+    "tc_p_error_curriculum": [_vp, _vp, _vp, _vp, _c.c_uint32, _c.c_uint32, _c.c_uint32, _i, _i, _u64, _i64, _i64, _vp],
     "tc_transitions": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i64, _vp],
     "tc_td_priorities": [_vp, _vp, _vp, _vp, _c.c_float, _vp, _i64, _vp],
     "tc_segmented_max": [_vp, _vp, _i, _vp, _vp, _i64, _vp],

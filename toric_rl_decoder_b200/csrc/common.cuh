@@ -72,6 +72,7 @@ __host__ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 //   first   0x40000000 | attempt                         attempt < 2^20 -> payload < 2^29          (sampler.cuh)
 //   select  0x60000000 | step                            step masked to 29 bits                    (policy_kernels.cuh)
 //   fixed   0x80000000 | attempt<<20 | draw              attempt < 2^9, draw < 2^20 -> < 2^30      (sampler.cuh)
+//   p-error 0xA0000000                                   no payload: one draw per (env, episode)   (policy_kernels.cuh)
 //   action  0xC0000000 | step                            both tag bits set: OR-ing cannot leave it (state_kernels.cuh)
 // (ABI 5 had select on 0x40000000 as well: the epsilon draw of (episode E, step 0) was the block of the first-error
 // draw, attempt 0, of the conditioned reset that opens episode E -- an exploratory first action forced U < eps and
@@ -80,6 +81,7 @@ constexpr uint32_t kDomField = 0x00000000u;    // depolarizing field slots / cod
 constexpr uint32_t kDomFirst = 0x40000000u;    // first-error draw of the conditioned sampler
 constexpr uint32_t kDomSelect = 0x60000000u;   // epsilon-greedy draws of tc_select_action
 constexpr uint32_t kDomFixed = 0x80000000u;    // fixed-weight sampler draws
+constexpr uint32_t kDomPError = 0xA0000000u;   // p_error curriculum draw ('random' strategy) of tc_p_error_curriculum
 constexpr uint32_t kDomAction = 0xC0000000u;   // random-policy action draws
 constexpr uint32_t kSelectStepMask = 0x1fffffffu;
 constexpr uint32_t kMaxAttempts = 1u << 20;    // depolarizing rejection attempts
@@ -89,7 +91,8 @@ constexpr uint32_t kMaxFixedAttempts = 1u << 9;
 static_assert(((kMaxAttempts - 1) << 10 | 0x3ffu) < kDomFirst, "field payload runs into the next domain");
 static_assert((kDomFirst | (kMaxAttempts - 1)) < kDomSelect, "first-error payload runs into the select domain");
 static_assert((kDomSelect | kSelectStepMask) < kDomFixed, "select payload runs into the fixed-weight domain");
-static_assert((kDomFixed | ((kMaxFixedAttempts - 1) << 20) | 0xfffffu) < kDomAction, "fixed-weight payload too wide");
+static_assert((kDomFixed | ((kMaxFixedAttempts - 1) << 20) | 0xfffffu) < kDomPError, "fixed-weight payload too wide");
+static_assert(kDomPError < kDomAction, "p-error domain below the action domain");
 static_assert((kMaxFixedAttempts - 1) <= 511u, "the fixed-weight counter has 9 attempt bits");
 static_assert((kDomAction >> 30) == 3u, "the action domain must own both tag bits (its step is OR-ed in unmasked)");
 constexpr int kSampleOneDraw = 16;             // TC_SAMPLE_ONE_DRAW (OR-ed into the sampling mode)

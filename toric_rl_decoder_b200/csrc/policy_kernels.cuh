@@ -158,4 +158,32 @@ segmented_max_kernel(const float* __restrict__ q, const int64_t* __restrict__ of
   if (lane == 0) out[e] = best;
 }
 
+// The p_error curriculum of the reference's actor (src/Actor_mp.py:171-181; parameters Distributed_mp.py:53-56,186-189)
+// in threshold units T = floor(p * 2^32): on every reset the env's ceiling grows, cap <- min(final, cap + delta), and
+// the p of the new episode is the ceiling ('linear') or uniform on [start, cap] ('random').  One thread per env.  Run
+// right after the fused step: an env whose steps[e] == 0 was auto-reset in that step and now receives the ceiling and
+// the p_thresh of its NEXT reset (all != 0: every env, to prime the first one) -- the k-th reset of an env therefore
+// uses exactly the reference's k-th ceiling, drawn one episode ahead of time.  The 'random' draw is
+// Philox(env id, episode[e], kDomPError).x scaled to the integer interval [min(start, cap), cap].
+__global__ void __launch_bounds__(256)
+p_error_curriculum_kernel(const int32_t* __restrict__ steps, const uint32_t* __restrict__ episode,
+                          uint32_t* __restrict__ p_cap, uint32_t* __restrict__ p_thresh, uint32_t start_t,
+                          uint32_t delta_t, uint32_t final_t, int random, int all, uint2 key, int64_t env_base,
+                          int64_t n) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  if (!all && steps[e] != 0) return;
+  const unsigned long long grown = (unsigned long long)p_cap[e] + (unsigned long long)delta_t;
+  const uint32_t cap = grown < (unsigned long long)final_t ? (uint32_t)grown : final_t;
+  p_cap[e] = cap;
+  uint32_t p = cap;
+  if (random) {
+    const uint32_t lo = start_t < cap ? start_t : cap;
+    const uint64_t env_id = (uint64_t)(env_base + e);
+    const uint4 rnd = philox4x32_10(make_uint4((uint32_t)env_id, (uint32_t)(env_id >> 32), episode[e], kDomPError), key);
+    p = lo + (uint32_t)(((unsigned long long)rnd.x * ((unsigned long long)(cap - lo) + 1ull)) >> 32);
+  }
+  p_thresh[e] = p;
+}
+
 }  // namespace tc

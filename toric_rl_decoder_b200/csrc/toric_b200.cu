@@ -1115,6 +1115,18 @@ int tc_select_action(const float* q_values, const uint8_t* pos, const int64_t* o
   return launch_status();
 }
 
+int tc_p_error_curriculum(const int32_t* steps, const uint32_t* episode, uint32_t* p_cap, uint32_t* p_thresh,
+                           uint32_t start_thresh, uint32_t delta_thresh, uint32_t final_thresh, int random_strategy,
+                           int all_envs, uint64_t seed, int64_t env_base, int64_t n, void* stream) {
+  if (n < 0) return -1;
+  if (n == 0) return 0;
+  if (!steps || !episode || !p_cap || !p_thresh) return -1;
+  p_error_curriculum_kernel<<<grid_for(n, 256), 256, 0, (cudaStream_t)stream>>>(
+      steps, episode, p_cap, p_thresh, start_thresh, delta_thresh, final_thresh, random_strategy, all_envs,
+      make_key(seed), env_base, n);
+  return launch_status();
+}
+
 int tc_transitions(const uint32_t* syn_prev, const uint32_t* syn_next, const int32_t* actions, void* out_prev,
                    void* out_next, int32_t* action_out, int out_dtype, int d, int64_t n, void* stream) {
   if (bad_d(d) || n < 0) return -1;

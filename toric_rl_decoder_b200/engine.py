@@ -253,7 +253,35 @@ class ToricEngine:
 
     def actor_step(self, *args, **kwargs):
         with _Range("toric/actor_step", self.nvtx):
-            return self._actor_step(*args, **kwargs)
+            res = self._actor_step(*args, **kwargs)
+            if self._curriculum is not None and kwargs.get("auto_reset", True):
+                self._curriculum_update(False)
+            return res
+
+    # -- p_error curriculum of the reference's actor (src/Actor_mp.py:43-47,171-181) ---------------------------------
+    _curriculum = None
+
+    def set_p_error_curriculum(self, start, final, delta, strategy="linear"):
+        """Every auto-reset of `actor_step` raises the env's p_error ceiling by `delta` up to `final` and draws the new
+        episode's p_error as the ceiling ('linear') or uniformly on [start, ceiling] ('random'), as the reference's
+        actor does on the host (env_p_error_start / _final / _delta / _strategy, Distributed_mp.py:53-56).  Call after
+        the initial reset; start=None switches it off.  The ceilings live in `self.p_cap` (thresholds)."""
+        if start is None:
+            self._curriculum = None
+            return
+        if strategy not in ("linear", "random"):
+            raise ValueError("strategy must be 'linear' or 'random'")
+        t = [int(p_to_thresh(float(x))) for x in (start, delta, final)]
+        self._curriculum = (t[0], t[1], t[2], 1 if strategy == "random" else 0)
+        self.p_cap = torch.from_numpy(np.full(self.n, t[0], dtype=np.uint32).view(np.int32)).to(self.device)
+        self._curriculum_update(True)
+
+    def _curriculum_update(self, all_envs):
+        s, dl, f, rnd = self._curriculum
+        _lib.check(self.lib.tc_p_error_curriculum(_ptr(self.steps), _ptr(self.episode), _ptr(self.p_cap),
+                                                  _ptr(self.p_thresh), s, dl, f, rnd, 1 if all_envs else 0, self.seed,
+                                                  self.env_base, self.n, _stream(self.device)),
+                   "tc_p_error_curriculum")
 
     def _actor_step(self, actions=None, auto_reset=True, mode=SAMPLE_DEPOLARIZING, n_fixed=0, keep_prev=False,
                     freeze_done=False, actions_buffer=None, results=None, between=None):
